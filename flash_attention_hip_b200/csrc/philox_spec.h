@@ -1,0 +1,98 @@
+/*
+ * philox_spec.h -- the ONE written dropout specification, shared verbatim by
+ * the CUDA kernels (csrc/) and by the CPU oracle (oracle/attn_oracle.c).
+ *
+ * The reference header passes `seed` and `offset` by value
+ * (/root/reference/flash_attn.h:33-34, :96-97) and says nothing about how they
+ * map to a mask.  This file is that mapping ("dropout
+ * RNG mapping"); "bit-exact dropout" means: every implementation in this repo
+ * reproduces fa_dropout_keep() below for every (b, h, row, col).
+ *
+ * Generator: Philox-4x32-10 (Salmon et al., SC'11), standard constants.
+ *
+ * Mapping, on ABSOLUTE coordinates so it cannot depend on tile shapes or
+ * thread layouts:
+ *   key     = { lo32(seed) ^ hi32(offset), hi32(seed) }
+ *   counter = { row, col / 16, b * num_heads + h, lo32(offset) }
+ *       row = query index inside its sequence, col = key index inside its
+ *       sequence, b = batch index inside this call, h = query head.
+ *   One Philox call yields 4 x 32 bits = 16 bytes, little-endian; attention
+ *   entry (row, col) owns byte (col % 16):
+ *       byte = (out[(col % 16) / 4] >> (8 * (col % 4))) & 0xff
+ *   keep  <=>  byte < T,   T = fa_dropout_threshold(p_dropout)
+ *       T = floor((1 - p_dropout) * 256 + 0.5) clamped to [0, 256]
+ *   Kept probabilities are scaled by 1 / (1 - p_dropout) (0 when p_dropout == 1).
+ *
+ * Plain C99; compiles under gcc, g++ and nvcc (host and device).
+ */
+#ifndef FA_B200_PHILOX_SPEC_H_
+#define FA_B200_PHILOX_SPEC_H_
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define FA_HD __host__ __device__ __forceinline__
+#else
+#define FA_HD static inline
+#endif
+
+#define FA_PHILOX_M0 0xD2511F53u
+#define FA_PHILOX_M1 0xCD9E8D57u
+#define FA_PHILOX_W0 0x9E3779B9u
+#define FA_PHILOX_W1 0xBB67AE85u
+#define FA_PHILOX_ROUNDS 10
+#define FA_DROPOUT_COLS_PER_CALL 16
+
+typedef struct { uint32_t v[4]; } fa_philox4_t;
+
+/* Philox-4x32 with FA_PHILOX_ROUNDS rounds. */
+FA_HD fa_philox4_t fa_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                 uint32_t k0, uint32_t k1) {
+  for (int r = 0; r < FA_PHILOX_ROUNDS; ++r) {
+    const uint64_t p0 = (uint64_t)FA_PHILOX_M0 * c0;
+    const uint64_t p1 = (uint64_t)FA_PHILOX_M1 * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    const uint32_t n1 = (uint32_t)p1;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    const uint32_t n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += FA_PHILOX_W0;
+    k1 += FA_PHILOX_W1;
+  }
+  fa_philox4_t out;
+  out.v[0] = c0; out.v[1] = c1; out.v[2] = c2; out.v[3] = c3;
+  return out;
+}
+
+/* Keep threshold T in [0, 256]: an entry is kept iff its byte < T. */
+FA_HD uint32_t fa_dropout_threshold(float p_dropout) {
+  float t = (1.0f - p_dropout) * 256.0f + 0.5f;
+  if (t < 0.0f) t = 0.0f;
+  if (t > 256.0f) t = 256.0f;
+  return (uint32_t)t;
+}
+
+/* 1/(1-p), or 0 when everything is dropped. */
+FA_HD float fa_dropout_rescale(float p_dropout) {
+  const float keep = 1.0f - p_dropout;
+  return keep > 0.0f ? 1.0f / keep : 0.0f;
+}
+
+/* The 16 random bytes shared by columns [16*colblk, 16*colblk+16) of one row. */
+FA_HD fa_philox4_t fa_dropout_bytes16(uint64_t seed, uint64_t offset, uint32_t bh,
+                                      uint32_t row, uint32_t colblk) {
+  const uint32_t k0 = (uint32_t)seed ^ (uint32_t)(offset >> 32);
+  const uint32_t k1 = (uint32_t)(seed >> 32);
+  return fa_philox4x32(row, colblk, bh, (uint32_t)offset, k0, k1);
+}
+
+/* Reference predicate: 1 = keep, 0 = drop.  bh = b * num_heads + h. */
+FA_HD int fa_dropout_keep(uint64_t seed, uint64_t offset, uint32_t bh, uint32_t row,
+                          uint32_t col, uint32_t threshold) {
+  const fa_philox4_t r = fa_dropout_bytes16(seed, offset, bh, row, col / FA_DROPOUT_COLS_PER_CALL);
+  const uint32_t within = col % FA_DROPOUT_COLS_PER_CALL;
+  const uint32_t byte = (r.v[within >> 2] >> (8u * (within & 3u))) & 0xffu;
+  return byte < threshold;
+}
+
+#endif /* FA_B200_PHILOX_SPEC_H_ */
