@@ -1,0 +1,214 @@
+"""Host-side mirror of the flash_attn.h operator interface (ctypes over the C ABI).
+
+Every function here ends in one call through libflash_attn.so's exported
+symbols -- the same six names the reference header declares
+(/root/reference/flash_attn.h:10-138).  torch is used only for device memory
+and streams.  There is no CPU path: a missing library or a failed call raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Tuple
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libflash_attn.so")
+
+PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = 0, 1, 2
+
+_lib = None
+
+_vp, _i, _f, _b, _u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_bool, ctypes.c_uint64
+
+# argument lists in the reference's order (reference flash_attn.h:10-36, :38-66, :68-99, :101-134)
+_FWD = [_vp] * 7 + [_i] * 9 + [_f] * 3 + [_b] * 3 + [_vp, _u64, _u64, _vp, _vp]
+_VFWD = [_vp] * 9 + [_i] * 9 + [_f] * 3 + [_b] * 3 + [_vp, _u64, _u64, _vp, _vp]
+_BWD = [_vp] * 12 + [_i] * 9 + [_f] * 3 + [_b] * 2 + [_i, _vp, _u64, _u64, _vp, _vp]
+_VBWD = [_vp] * 14 + [_i] * 9 + [_f] * 3 + [_b] * 2 + [_i, _vp, _u64, _u64, _vp, _vp]
+assert (len(_FWD), len(_VFWD), len(_BWD), len(_VBWD)) == (27, 29, 32, 34)
+
+
+class FlashAttnError(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Loads the C-ABI library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FlashAttnError(
+                f"{LIB_PATH} is missing: run `python -m flash_attention_hip_b200.build` "
+                "(there is no fallback path)")
+        l = ctypes.CDLL(LIB_PATH)
+        for name, args in (("flash_attn_fwd", _FWD), ("flash_attn_varlen_fwd", _VFWD),
+                           ("flash_attn_bwd", _BWD), ("flash_attn_varlen_bwd", _VBWD)):
+            fn = getattr(l, name)
+            fn.argtypes = args
+            fn.restype = ctypes.c_bool
+        l.flash_attn_error.restype = ctypes.c_char_p
+        l.flash_attn_set_error.argtypes = [ctypes.c_char_p]
+        l.flash_attn_b200_version.restype = ctypes.c_char_p
+        l.flash_attn_b200_set_path.argtypes = [_i]
+        _lib = l
+    return _lib
+
+
+def last_error() -> str:
+    return lib().flash_attn_error().decode()
+
+
+def set_path(path: int) -> None:
+    lib().flash_attn_b200_set_path(path)
+
+
+def last_path() -> int:
+    return int(lib().flash_attn_b200_last_path())
+
+
+def last_launch_count() -> int:
+    return int(lib().flash_attn_b200_last_launch_count())
+
+
+def round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _check(ok: bool, what: str):
+    if not ok:
+        raise FlashAttnError(f"{what} failed: {last_error()}")
+
+
+def _stream_ptr(stream: Optional[torch.cuda.Stream]):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return ctypes.c_void_p(s.cuda_stream)
+
+
+def _mask_args(attn_mask: Optional[torch.Tensor]):
+    if attn_mask is None:
+        return None, None, None
+    assert attn_mask.dim() == 4 and attn_mask.is_contiguous()
+    dims = (ctypes.c_int64 * 4)(*attn_mask.shape)
+    return _ptr(attn_mask), ctypes.cast(dims, ctypes.c_void_p), dims
+
+
+def flash_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, p_dropout: float = 0.0,
+                   softmax_scale: Optional[float] = None, is_causal: bool = False,
+                   return_softmax: bool = False, seed: int = 0, offset: int = 0,
+                   attn_mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                   stream: Optional[torch.cuda.Stream] = None):
+    """Dense forward.  q [b, sq, h, d]; k, v [b, sk, hk, d]; fp16 or bf16, contiguous.
+    Returns (out, softmax_lse [b, h, sq] fp32, softmax or None, rng_state [2] int64)."""
+    assert q.is_cuda and q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
+    assert q.dtype in (torch.float16, torch.bfloat16) and k.dtype == q.dtype and v.dtype == q.dtype
+    b, sq, h, d = q.shape
+    _, sk, hk, _ = k.shape
+    scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
+    sq_r, sk_r, d_r = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+    if out is None:
+        out = torch.empty_like(q)
+    lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
+    sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
+    rng = torch.empty(2, dtype=torch.int64, device=q.device)
+    mptr, mdims, _keep = _mask_args(attn_mask)
+    ok = lib().flash_attn_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse),
+                              b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+                              1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
+                              q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset, mptr, mdims)
+    _check(ok, "flash_attn_fwd")
+    return out, lse, sm, rng
+
+
+def flash_attn_varlen_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
+                          cu_seqlens_q: torch.Tensor, cu_seqlens_k: torch.Tensor,
+                          max_seqlen_q: int, max_seqlen_k: int, *, p_dropout: float = 0.0,
+                          softmax_scale: Optional[float] = None, is_causal: bool = False,
+                          return_softmax: bool = False, seed: int = 0, offset: int = 0,
+                          out: Optional[torch.Tensor] = None,
+                          stream: Optional[torch.cuda.Stream] = None):
+    """Packed forward.  q [total_q, h, d]; k, v [total_k, hk, d]; cu_seqlens int32 [b+1] on device.
+    Returns (out, softmax_lse [b, h, max_seqlen_q], softmax or None, rng_state)."""
+    assert q.is_cuda and q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
+    assert cu_seqlens_q.dtype == torch.int32 and cu_seqlens_k.dtype == torch.int32
+    _, h, d = q.shape
+    _, hk, _ = k.shape
+    b = cu_seqlens_q.numel() - 1
+    scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
+    sq_r, sk_r, d_r = round_up(max_seqlen_q, 128), round_up(max_seqlen_k, 128), round_up(d, 32)
+    if out is None:
+        out = torch.empty_like(q)
+    lse = torch.full((b, h, max_seqlen_q), float("inf"), dtype=torch.float32, device=q.device)
+    sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
+    rng = torch.empty(2, dtype=torch.int64, device=q.device)
+    ok = lib().flash_attn_varlen_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k),
+                                     _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse), b, max_seqlen_q,
+                                     max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+                                     1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
+                                     q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset,
+                                     None, None)
+    _check(ok, "flash_attn_varlen_fwd")
+    return out, lse, sm, rng
+
+
+def _bwd_scratch(b, sq_r, h, d_r, device):
+    softmax_d = torch.empty((b, h, sq_r), dtype=torch.float32, device=device)
+    dq_accum = torch.empty((b, sq_r, h, d_r), dtype=torch.float32, device=device)
+    return softmax_d, dq_accum
+
+
+def flash_attn_bwd(dout, q, k, v, out, softmax_lse, *, p_dropout: float = 0.0,
+                   softmax_scale: Optional[float] = None, is_causal: bool = False,
+                   deterministic: bool = False, seed: int = 0, offset: int = 0,
+                   attn_mask: Optional[torch.Tensor] = None, scratch=None,
+                   grads: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
+                   stream: Optional[torch.cuda.Stream] = None):
+    """Dense backward; returns (dq, dk, dv).  seed/offset must be the forward's."""
+    for t in (dout, q, k, v, out):
+        assert t.is_cuda and t.is_contiguous()
+    b, sq, h, d = q.shape
+    _, sk, hk, _ = k.shape
+    scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
+    sq_r, sk_r, d_r = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
+    softmax_d, dq_accum = scratch if scratch is not None else _bwd_scratch(b, sq_r, h, d_r, q.device)
+    dq, dk, dv = grads if grads is not None else (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
+    mptr, mdims, _keep = _mask_args(attn_mask)
+    ok = lib().flash_attn_bwd(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
+                              _ptr(softmax_lse), None, _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum),
+                              b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+                              1.0 / scale if scale != 0 else 0.0, is_causal,
+                              q.dtype == torch.bfloat16, 1 if deterministic else 0,
+                              _stream_ptr(stream), seed, offset, mptr, mdims)
+    _check(ok, "flash_attn_bwd")
+    return dq, dk, dv
+
+
+def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k,
+                          max_seqlen_q: int, max_seqlen_k: int, *, p_dropout: float = 0.0,
+                          softmax_scale: Optional[float] = None, is_causal: bool = False,
+                          deterministic: bool = False, seed: int = 0, offset: int = 0,
+                          stream: Optional[torch.cuda.Stream] = None):
+    """Packed backward; returns (dq, dk, dv)."""
+    for t in (dout, q, k, v, out):
+        assert t.is_cuda and t.is_contiguous()
+    _, h, d = q.shape
+    _, hk, _ = k.shape
+    b = cu_seqlens_q.numel() - 1
+    scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
+    sq_r, sk_r, d_r = round_up(max_seqlen_q, 128), round_up(max_seqlen_k, 128), round_up(d, 32)
+    softmax_d, dq_accum = _bwd_scratch(b, sq_r, h, d_r, q.device)
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    ok = lib().flash_attn_varlen_bwd(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
+                                     _ptr(softmax_lse), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), None,
+                                     _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum), b, max_seqlen_q,
+                                     max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+                                     1.0 / scale if scale != 0 else 0.0, is_causal,
+                                     q.dtype == torch.bfloat16, 1 if deterministic else 0,
+                                     _stream_ptr(stream), seed, offset, None, None)
+    _check(ok, "flash_attn_varlen_bwd")
+    return dq, dk, dv

@@ -1,0 +1,281 @@
+// fa_api.cu -- the C ABI of include/flash_attn.h: validation, parameter block,
+// kernel-family choice.  Each entry point replaces the reference prototype of
+// the same name (reference flash_attn.h:10, :38, :68, :101, :136, :138).
+//
+// There is no CPU fallback: every path ends in a CUDA launch or in `false`.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/flash_attn.h"
+#include "../../include/flash_attn_b200_ext.h"
+#include "fa_common.cuh"
+
+namespace {
+
+thread_local std::string g_error;
+thread_local int g_path_request = FA_B200_PATH_AUTO;
+thread_local int g_last_path = 0;
+thread_local int g_last_launches = 0;
+
+bool fail(const char *fmt, ...) __attribute__((format(printf, 1, 2)));
+bool fail(const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  flash_attn_set_error(buf);
+  return false;
+}
+
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+__global__ void write_rng_state_kernel(uint64_t *dst, uint64_t seed, uint64_t offset) {
+  dst[0] = seed;
+  dst[1] = offset;
+}
+
+struct Shape {
+  int b, sq, sk, sq_r, sk_r, h, hk, d, d_r;
+};
+
+// Checks shared by the four entry points.  Returns false after set_error.
+bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout, float softmax_scale,
+                 bool is_causal, bool is_bf16, uint64_t seed, uint64_t offset,
+                 const int32_t *cu_q, const int32_t *cu_k, bool varlen, const void *attn_mask,
+                 const int64_t *mask_dims) {
+  if (s.b < 0 || s.sq < 0 || s.sk < 0) return fail("%s: negative batch_size or seqlen", fn);
+  if (s.h <= 0 || s.hk <= 0) return fail("%s: num_heads and num_heads_k must be positive", fn);
+  if (s.h % s.hk) return fail("%s: num_heads (%d) must be a multiple of num_heads_k (%d)", fn, s.h, s.hk);
+  if (s.d <= 0 || s.d > 256 || s.d % 8)
+    return fail("%s: head_size must be a multiple of 8 in [8, 256], got %d", fn, s.d);
+  if (!(p_dropout >= 0.f && p_dropout <= 1.f)) return fail("%s: p_dropout must be in [0, 1]", fn);
+  if (!std::isfinite(softmax_scale)) return fail("%s: softmax_scale must be finite", fn);
+  if (varlen && (!cu_q || !cu_k)) return fail("%s: cu_seqlens_q / cu_seqlens_k must not be NULL", fn);
+  if (s.b > 65535) return fail("%s: batch_size > 65535 is not supported", fn);
+  std::memset(&p, 0, sizeof(p));
+  p.b = s.b; p.sq = s.sq; p.sk = s.sk; p.sq_rounded = s.sq_r; p.sk_rounded = s.sk_r;
+  p.h = s.h; p.hk = s.hk; p.d = s.d; p.d_rounded = s.d_r;
+  p.scale = softmax_scale;
+  p.p_dropout = p_dropout;
+  p.rp_dropout = fa_dropout_rescale(p_dropout);
+  p.drop_threshold = fa_dropout_threshold(p_dropout);
+  p.seed = seed; p.offset = offset;
+  p.causal = is_causal; p.is_bf16 = is_bf16;
+  p.cu_q = varlen ? cu_q : nullptr;
+  p.cu_k = varlen ? cu_k : nullptr;
+  if (attn_mask) {
+    if (varlen) return fail("%s: attn_mask is not supported with packed (varlen) inputs", fn);
+    if (!mask_dims) return fail("%s: attn_mask given but mask_dims is NULL", fn);
+    if ((mask_dims[0] != 1 && mask_dims[0] != s.b) || (mask_dims[1] != 1 && mask_dims[1] != s.h) ||
+        mask_dims[2] != s.sq || mask_dims[3] != s.sk)
+      return fail("%s: mask_dims must be {1|batch, 1|num_heads, seqlen_q, seqlen_k}", fn);
+    p.mask = attn_mask;
+    p.mask_b = mask_dims[0]; p.mask_h = mask_dims[1]; p.mask_sq = mask_dims[2]; p.mask_sk = mask_dims[3];
+  }
+  return true;
+}
+
+bool fwd_impl(const char *fn, const void *q, const void *k, const void *v, const int32_t *cu_q,
+              const int32_t *cu_k, bool varlen, void *rng_state, void *out, void *softmax_ptr,
+              void *softmax_lse_ptr, const Shape &s, float p_dropout, float softmax_scale,
+              bool is_causal, bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
+              uint64_t offset, const void *attn_mask, const int64_t *mask_dims) {
+  fa::Params p;
+  if (!fill_common(p, fn, s, p_dropout, softmax_scale, is_causal, is_bf16, seed, offset, cu_q, cu_k,
+                   varlen, attn_mask, mask_dims))
+    return false;
+  const bool empty = s.b == 0 || s.sq == 0;
+  if (!empty && (!q || !k || !v || !out || !softmax_lse_ptr))
+    return fail("%s: q, k, v, out and softmax_lse_ptr must not be NULL", fn);
+  if (!aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(out))
+    return fail("%s: q, k, v, out must be 16-byte aligned", fn);
+  if (return_softmax) {
+    if (!softmax_ptr) return fail("%s: return_softmax set but softmax_ptr is NULL", fn);
+    if (s.sq_r < s.sq || s.sk_r < s.sk)
+      return fail("%s: seqlen_q_rounded/seqlen_k_rounded smaller than the sequence lengths", fn);
+  }
+  p.q = q; p.k = k; p.v = v; p.out = out;
+  p.lse = static_cast<float *>(softmax_lse_ptr);
+  p.softmax_ret = return_softmax ? softmax_ptr : nullptr;
+
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int launches = 0;
+  if (rng_state) {
+    write_rng_state_kernel<<<1, 1, 0, st>>>(static_cast<uint64_t *>(rng_state), seed, offset);
+    ++launches;
+  }
+  if (empty) { g_last_launches = launches; return true; }
+
+  const bool tc_ok = fa::tc_fwd_supported(p);
+  if (g_path_request == FA_B200_PATH_TCGEN05 && !tc_ok)
+    return fail("%s: tcgen05 path requested but this problem is outside it", fn);
+  const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
+  const char *err = use_tc ? fa::launch_tc_fwd(p, st) : fa::launch_generic_fwd(p, st);
+  if (err) return fail("%s: %s", fn, err);
+  g_last_path = use_tc ? FA_B200_PATH_TCGEN05 : FA_B200_PATH_GENERIC;
+  g_last_launches = launches + 1;
+  return true;
+}
+
+bool bwd_impl(const char *fn, const void *dout, const void *q, const void *k, const void *v,
+              const void *out, const void *softmax_d, const void *softmax_lse, const int32_t *cu_q,
+              const int32_t *cu_k, bool varlen, void *dq, void *dk, void *dv, void *dq_accum,
+              const Shape &s, float p_dropout, float softmax_scale, bool is_causal, bool is_bf16,
+              int num_splits, fa_stream_t stream, uint64_t seed, uint64_t offset,
+              const void *attn_mask, const int64_t *mask_dims) {
+  fa::Params p;
+  if (!fill_common(p, fn, s, p_dropout, softmax_scale, is_causal, is_bf16, seed, offset, cu_q, cu_k,
+                   varlen, attn_mask, mask_dims))
+    return false;
+  if (s.b == 0) { g_last_launches = 0; return true; }
+  if (!dout || !q || !k || !v || !out || !softmax_d || !softmax_lse || !dq || !dk || !dv)
+    return fail("%s: dout, q, k, v, out, softmax_d, softmax_lse, dq, dk, dv must not be NULL", fn);
+  if (!aligned16(dout) || !aligned16(q) || !aligned16(k) || !aligned16(v) || !aligned16(out) ||
+      !aligned16(dq) || !aligned16(dk) || !aligned16(dv))
+    return fail("%s: tensors must be 16-byte aligned", fn);
+  if (s.sq_r < s.sq) return fail("%s: seqlen_q_rounded smaller than seqlen_q", fn);
+  p.dout = dout; p.q = q; p.k = k; p.v = v; p.out = const_cast<void *>(out);
+  p.softmax_d = const_cast<float *>(static_cast<const float *>(softmax_d));
+  p.lse = const_cast<float *>(static_cast<const float *>(softmax_lse));
+  p.dq = dq; p.dk = dk; p.dv = dv;
+  p.dq_accum = static_cast<float *>(dq_accum);
+  p.deterministic = num_splits == 1;
+
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool tc_ok = fa::tc_bwd_supported(p);
+  if (g_path_request == FA_B200_PATH_TCGEN05 && !tc_ok)
+    return fail("%s: tcgen05 path requested but this problem is outside it", fn);
+  const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
+  const char *err = fa::launch_bwd_preprocess(p, st);
+  if (!err) err = use_tc ? fa::launch_tc_bwd(p, st) : fa::launch_generic_bwd(p, st);
+  if (err) return fail("%s: %s", fn, err);
+  g_last_path = use_tc ? FA_B200_PATH_TCGEN05 : FA_B200_PATH_GENERIC;
+  g_last_launches = 3;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Replaces reference flash_attn.h:10-36.
+bool flash_attn_fwd(const void *const q, const void *const k, const void *const v,
+                    void *const rng_state, void *const out, void *const softmax_ptr,
+                    void *const softmax_lse_ptr, const int batch_size, const int seqlen_q,
+                    const int seqlen_k, const int seqlen_q_rounded, const int seqlen_k_rounded,
+                    const int num_heads, const int num_heads_k, const int head_size,
+                    const int head_size_rounded, const float p_dropout, const float softmax_scale,
+                    const float softmax_unscale, const bool is_causal, const bool return_softmax,
+                    const bool is_bf16, fa_stream_t stream, uint64_t seed, uint64_t offset,
+                    const void *const attn_mask, const int64_t *const mask_dims) {
+  (void)softmax_unscale;  // the bias is added after scaling q.k, so 1/scale is never needed
+  try {
+    const Shape s{batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return fwd_impl("flash_attn_fwd", q, k, v, nullptr, nullptr, false, rng_state, out, softmax_ptr,
+                    softmax_lse_ptr, s, p_dropout, softmax_scale, is_causal, return_softmax, is_bf16,
+                    stream, seed, offset, attn_mask, mask_dims);
+  } catch (...) {
+    return fail("flash_attn_fwd: unexpected exception");
+  }
+}
+
+// Replaces reference flash_attn.h:38-66.
+bool flash_attn_varlen_fwd(const void *const q, const void *const k, const void *const v,
+                           const int32_t *const cu_seqlens_q, const int32_t *const cu_seqlens_k,
+                           void *const rng_state, void *const out, void *const softmax_ptr,
+                           void *const softmax_lse_ptr, const int batch_size,
+                           const int max_seqlen_q, const int max_seqlen_k,
+                           const int seqlen_q_rounded, const int seqlen_k_rounded,
+                           const int num_heads, const int num_heads_k, const int head_size,
+                           const int head_size_rounded, const float p_dropout,
+                           const float softmax_scale, const float softmax_unscale,
+                           const bool is_causal, const bool return_softmax, const bool is_bf16,
+                           fa_stream_t stream, uint64_t seed, uint64_t offset,
+                           const void *const attn_mask, const void *const mask_dims) {
+  (void)softmax_unscale;
+  try {
+    const Shape s{batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return fwd_impl("flash_attn_varlen_fwd", q, k, v, cu_seqlens_q, cu_seqlens_k, true, rng_state,
+                    out, softmax_ptr, softmax_lse_ptr, s, p_dropout, softmax_scale, is_causal,
+                    return_softmax, is_bf16, stream, seed, offset, attn_mask,
+                    static_cast<const int64_t *>(mask_dims));
+  } catch (...) {
+    return fail("flash_attn_varlen_fwd: unexpected exception");
+  }
+}
+
+// Replaces reference flash_attn.h:68-99.
+bool flash_attn_bwd(const void *const dout, const void *const q, const void *const k,
+                    const void *const v, const void *const out, const void *const softmax_d,
+                    const void *const softmax_lse, void *const rng_state, void *const dq,
+                    void *const dk, void *const dv, void *const dq_accum, const int batch_size,
+                    const int seqlen_q, const int seqlen_k, const int seqlen_q_rounded,
+                    const int seqlen_k_rounded, const int num_heads, const int num_heads_k,
+                    const int head_size, const int head_size_rounded, const float p_dropout,
+                    const float softmax_scale, const float softmax_unscale, const bool is_causal,
+                    const bool is_bf16, const int num_splits, fa_stream_t stream, uint64_t seed,
+                    uint64_t offset, const void *const attn_mask, const int64_t *const mask_dims) {
+  (void)softmax_unscale;
+  (void)rng_state;  // seed/offset arrive by value (reference flash_attn.h:96-97)
+  try {
+    const Shape s{batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return bwd_impl("flash_attn_bwd", dout, q, k, v, out, softmax_d, softmax_lse, nullptr, nullptr,
+                    false, dq, dk, dv, dq_accum, s, p_dropout, softmax_scale, is_causal, is_bf16,
+                    num_splits, stream, seed, offset, attn_mask, mask_dims);
+  } catch (...) {
+    return fail("flash_attn_bwd: unexpected exception");
+  }
+}
+
+// Replaces reference flash_attn.h:101-134.
+bool flash_attn_varlen_bwd(const void *const dout, const void *const q, const void *const k,
+                           const void *const v, const void *const out,
+                           const void *const softmax_d, const void *const softmax_lse,
+                           const int32_t *const cu_seqlens_q, const int32_t *const cu_seqlens_k,
+                           void *const rng_state, void *const dq, void *const dk, void *const dv,
+                           void *const dq_accum, const int batch_size, const int max_seqlen_q,
+                           const int max_seqlen_k, const int seqlen_q_rounded,
+                           const int seqlen_k_rounded, const int num_heads, const int num_heads_k,
+                           const int head_size, const int head_size_rounded, const float p_dropout,
+                           const float softmax_scale, const float softmax_unscale,
+                           const bool is_causal, const bool is_bf16, const int num_splits,
+                           fa_stream_t stream, uint64_t seed, uint64_t offset,
+                           const void *attn_mask, const int64_t *const mask_dims) {
+  (void)softmax_unscale;
+  (void)rng_state;
+  try {
+    const Shape s{batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return bwd_impl("flash_attn_varlen_bwd", dout, q, k, v, out, softmax_d, softmax_lse,
+                    cu_seqlens_q, cu_seqlens_k, true, dq, dk, dv, dq_accum, s, p_dropout,
+                    softmax_scale, is_causal, is_bf16, num_splits, stream, seed, offset, attn_mask,
+                    mask_dims);
+  } catch (...) {
+    return fail("flash_attn_varlen_bwd: unexpected exception");
+  }
+}
+
+// Replaces reference flash_attn.h:136.  Thread-local.
+void flash_attn_set_error(const char *msg) {
+  try {
+    g_error = msg ? msg : "";
+  } catch (...) {
+  }
+}
+
+// Replaces reference flash_attn.h:138.
+const char *flash_attn_error(void) { return g_error.c_str(); }
+
+void flash_attn_b200_set_path(int path) { g_path_request = path; }
+int flash_attn_b200_last_path(void) { return g_last_path; }
+int flash_attn_b200_last_launch_count(void) { return g_last_launches; }
+const char *flash_attn_b200_version(void) { return "flash_attn_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// fa_common.cuh -- parameter block and small device helpers shared by every
+// kernel behind the flash_attn.h C ABI (include/flash_attn.h).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "philox_spec.h"
+
+namespace fa {
+
+// One attention problem, as the four ABI entry points describe it
+// (reference flash_attn.h:10-36, :38-66, :68-99, :101-134).
+struct Params {
+  // forward tensors
+  const void *q, *k, *v;
+  void *out;
+  float *lse;          // [b, h, seqlen_q]
+  void *softmax_ret;   // [b, h, sq_rounded, sk_rounded] or null
+  // backward tensors
+  const void *dout;
+  void *dq, *dk, *dv;
+  float *softmax_d;    // [b, h, sq_rounded]
+  float *dq_accum;     // [b, sq_rounded, h, d_rounded] scratch
+  // packed layout (null = dense)
+  const int32_t *cu_q, *cu_k;
+  // optional additive bias
+  const void *mask;
+  int64_t mask_b, mask_h, mask_sq, mask_sk;
+
+  int b, sq, sk;       // sq/sk: dense lengths or packed maxima
+  int sq_rounded, sk_rounded;
+  int h, hk, d, d_rounded;
+  float scale;         // softmax_scale
+  float p_dropout;
+  float rp_dropout;    // 1/(1-p)
+  uint32_t drop_threshold;  // keep iff byte < threshold
+  uint64_t seed, offset;
+  bool causal, is_bf16, deterministic;
+};
+
+// Per-sequence extents; dense and packed layouts differ only here.
+struct SeqInfo {
+  int q0, k0;   // first token row of this sequence in the [tokens, heads, d] view
+  int sq, sk;   // its lengths
+};
+
+__device__ __forceinline__ SeqInfo seq_info(const Params &p, int b) {
+  SeqInfo s;
+  if (p.cu_q) {
+    s.q0 = p.cu_q[b];
+    s.k0 = p.cu_k[b];
+    s.sq = p.cu_q[b + 1] - s.q0;
+    s.sk = p.cu_k[b + 1] - s.k0;
+  } else {
+    s.q0 = b * p.sq;
+    s.k0 = b * p.sk;
+    s.sq = p.sq;
+    s.sk = p.sk;
+  }
+  return s;
+}
+
+template <typename T> __device__ __forceinline__ float to_f32(T x);
+template <> __device__ __forceinline__ float to_f32<__half>(__half x) { return __half2float(x); }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 x) { return __bfloat162float(x); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float x);
+template <> __device__ __forceinline__ __half from_f32<__half>(float x) { return __float2half_rn(x); }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float x) { return __float2bfloat16_rn(x); }
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Launchers (defined in the .cu files; all asynchronous on `stream`).
+const char *launch_generic_fwd(const Params &p, cudaStream_t stream);
+const char *launch_generic_bwd(const Params &p, cudaStream_t stream);
+const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream);
+
+// tcgen05 paths; return nullptr on success, else a static error string.
+bool tc_fwd_supported(const Params &p);
+const char *launch_tc_fwd(const Params &p, cudaStream_t stream);
+bool tc_bwd_supported(const Params &p);
+const char *launch_tc_bwd(const Params &p, cudaStream_t stream);
+
+}  // namespace fa
