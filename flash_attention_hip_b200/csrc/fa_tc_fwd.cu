@@ -1,0 +1,427 @@
+// fa_tc_fwd.cu -- FlashAttention-2 forward for sm_100a: TMA -> shared memory,
+// tcgen05.mma with accumulators in tensor memory, online softmax in registers.
+// Implements flash_attn_fwd / flash_attn_varlen_fwd (reference flash_attn.h:10-66)
+// for head_size 64/128, fp16/bf16, causal or not, GQA, Philox dropout.
+//
+// One CTA owns 256 query rows of one (batch, head): two 128-row tiles that
+// ping-pong on the tensor pipe.  Twelve warps:
+//   warps 0-3   softmax of tile 0 (thread r owns query row r: TMEM lane r)
+//   warps 4-7   softmax of tile 1
+//   warp  8     tcgen05.mma issue (one lane); allocates/frees tensor memory
+//   warp  9     TMA producer (one lane)
+//   warps 10-11 idle (they only complete the warpgroup for setmaxnreg)
+// Tensor memory (512 columns x 128 lanes x 32 bit):
+//   [0,128) S0 | [128,256) S1 | [256,256+D) O0 | [384,384+D) O1
+//   P (bf16 pairs) overwrites columns [kPOff, kPOff+64) of its S tile.
+// Per KV tile j and query tile t, in tensor-pipe issue order:
+//   S_t = Q_t K_j^T            (A, B from shared memory, both K-major)
+//   softmax warps: S_t -> regs, mask, running max / sum, P_t -> TMEM
+//   O_t (+)= P_t V_j           (A from tensor memory, B MN-major from shared)
+// The running max is updated lazily: O_t is rescaled (by the softmax warps
+// themselves) only when the max grew by more than 2^8, which keeps P <= 256 in
+// bf16 and takes the rescale off the steady-state critical path.
+#include "fa_common.cuh"
+#include "ptx_sm100.cuh"
+#include "tma_host.cuh"
+
+namespace fa {
+
+namespace {
+
+constexpr int kTileM = 128;        // query rows per tile (= TMEM lanes)
+constexpr int kTileN = 128;        // keys per KV tile
+constexpr int kThreads = 384;
+constexpr int kMmaWarp = 8, kLoadWarp = 9;
+constexpr uint32_t kPOff = 32;     // P's first column inside its S tile
+constexpr float kRescaleThreshold = 8.0f;  // in log2 units
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+template <int D>
+struct Cfg {
+  static constexpr int kStages = D == 128 ? 2 : 4;            // K and V ring depth
+  static constexpr uint32_t kTileBytes = kTileM * D * 2;      // one Q/K/V tile
+  static constexpr uint32_t kSubBytes = kTileM * 128;         // one [128 x 64] swizzled sub-tile
+  static constexpr uint32_t kSmemQ = 0;
+  static constexpr uint32_t kSmemK = 2 * kTileBytes;
+  static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
+  static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
+  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 6;
+  static constexpr uint32_t kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;  // + alignment slack
+};
+
+struct Bars {
+  uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_full, pv_done;  // first of each group
+};
+
+__device__ __forceinline__ uint32_t pack_pair(float lo, float hi, bool bf16) {
+  if (bf16) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&v);
+  }
+  const __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t *>(&v);
+}
+
+// Turns 4 random bytes into two AND-masks for packed 16-bit pairs: byte k of
+// `w` keeps element k iff byte < T (csrc/philox_spec.h).  SWAR compare on the
+// low 7 bits, the top bit folded in, then PRMT's sign-replicate mode expands
+// the per-byte verdict (bit 7) to 16 bits.
+struct DropConst {
+  uint32_t add7;   // (0x80 - (T & 0x7f)) replicated
+  bool t_msb;      // T >= 128
+};
+__device__ __forceinline__ void keep_masks(uint32_t w, const DropConst &dc, uint32_t &m01, uint32_t &m23) {
+  const uint32_t ge7 = (w & 0x7f7f7f7fu) + dc.add7;           // bit7 of each byte: low7 >= T7
+  const uint32_t keep = dc.t_msb ? ~(w & ge7) : ~(w | ge7);   // bit7 of each byte: byte < T
+  m01 = __byte_perm(keep, 0, 0x9988);
+  m23 = __byte_perm(keep, 0, 0xbbaa);
+}
+
+}  // namespace
+
+namespace {
+
+struct TcFwdArgs {
+  void *out;
+  float *lse;
+  const int32_t *cu_q, *cu_k;
+  int b, sq, sk, h, hk;
+  float scale_log2;      // softmax_scale * log2(e)
+  float rp_dropout;
+  uint32_t drop_threshold;
+  uint32_t key0, key1, ctr3;   // Philox key / counter word 3 (csrc/philox_spec.h)
+  int causal;
+};
+
+template <int D, bool kBF16, bool kDropout>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+              const __grid_constant__ CUtensorMap tmap_v, const TcFwdArgs a) {
+  using C = Cfg<D>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sbase = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *sgen = smem_raw + (sbase - ptx::smem_u32(smem_raw));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- problem coordinates -------------------------------------------------
+  const int bidx = blockIdx.z, head = blockIdx.y;
+  const int qblk = a.causal ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;  // heavy first
+  int q0 = 0, k0 = 0, sq = a.sq, sk = a.sk, bcoord = bidx;
+  if (a.cu_q) {
+    q0 = a.cu_q[bidx]; k0 = a.cu_k[bidx];
+    sq = a.cu_q[bidx + 1] - q0; sk = a.cu_k[bidx + 1] - k0;
+    bcoord = 0;
+  }
+  const int m0 = qblk * 2 * kTileM;
+  if (m0 >= sq) return;                       // whole CTA leaves before any barrier
+  const int hk = head / (a.h / a.hk);
+  const int shift = sk - sq;                  // causal: key j visible to row i iff j <= i + shift
+  const int nkv = (sk + kTileN - 1) / kTileN;
+  int ntile[2];
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int r0 = m0 + t * kTileM;
+    int n = r0 < sq ? nkv : 0;
+    if (a.causal && n) {
+      const int last = min(r0 + kTileM, sq) - 1 + shift;   // last visible key of the tile
+      n = last < 0 ? 0 : min(nkv, last / kTileN + 1);
+    }
+    ntile[t] = n;
+  }
+  const int nmax = max(ntile[0], ntile[1]);
+  const bool has_tile1 = m0 + kTileM < sq;
+
+  // ---- barriers, tensor memory ----------------------------------------------
+  const uint32_t bar0 = sbase + C::kSmemBar;
+  Bars B;
+  B.q_full = bar0;
+  B.k_full = bar0 + 8;
+  B.k_empty = B.k_full + 8 * C::kStages;
+  B.v_full = B.k_empty + 8 * C::kStages;
+  B.v_empty = B.v_full + 8 * C::kStages;
+  B.s_full = B.v_empty + 8 * C::kStages;
+  B.p_full = B.s_full + 16;
+  B.pv_done = B.p_full + 16;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + C::kSmemBar + C::kNumBars * 8);
+
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(B.q_full, 1);
+    for (int s = 0; s < C::kStages; ++s) {
+      ptx::mbar_init(B.k_full + 8 * s, 1);
+      ptx::mbar_init(B.k_empty + 8 * s, 1);
+      ptx::mbar_init(B.v_full + 8 * s, 1);
+      ptx::mbar_init(B.v_empty + 8 * s, 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      ptx::mbar_init(B.s_full + 8 * t, 1);
+      ptx::mbar_init(B.p_full + 8 * t, kTileM);
+      ptx::mbar_init(B.pv_done + 8 * t, 1);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == kLoadWarp && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_q);
+    ptx::prefetch_tensormap(&tmap_k);
+    ptx::prefetch_tensormap(&tmap_v);
+  }
+  if (warp == kMmaWarp) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp >= 8) {
+    // ======================= producer warpgroup ================================
+    ptx::setmaxnreg_dec<40>();
+    if (warp == kLoadWarp && lane == 0) {
+      // ---- TMA producer --------------------------------------------------------
+      const int qrow = q0 * (a.cu_q ? 1 : 0) + m0;   // packed: absolute token row; dense: row in sequence
+      const int krow = k0 * (a.cu_q ? 1 : 0);
+      ptx::mbar_arrive_expect_tx(B.q_full, (has_tile1 ? 2 : 1) * C::kTileBytes);
+      for (int t = 0; t < (has_tile1 ? 2 : 1); ++t)
+        for (int c = 0; c < D / 64; ++c)
+          ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, &tmap_q, B.q_full,
+                           c * 64, head, qrow + t * kTileM, bcoord);
+      for (int j = 0; j < nmax; ++j) {
+        const int s = j % C::kStages;
+        const uint32_t ph = (j / C::kStages) & 1;
+        if (j >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
+        ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
+        for (int c = 0; c < D / 64; ++c)
+          ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, &tmap_k,
+                           B.k_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
+        if (j >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
+        ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
+        for (int c = 0; c < D / 64; ++c)
+          ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, &tmap_v,
+                           B.v_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
+      }
+    } else if (warp == kMmaWarp && lane == 0) {
+      // ---- MMA issuer ------------------------------------------------------------
+      constexpr uint32_t fmt = kBF16 ? ptx::kFmtBF16 : ptx::kFmtF16;
+      constexpr uint32_t idesc_qk = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorK, kTileM, kTileN);
+      constexpr uint32_t idesc_pv = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorMN, kTileM, D);
+      constexpr uint64_t hi_k = ptx::make_smem_desc_hi(16, 1024);             // K-major operands
+      constexpr uint64_t hi_mn = ptx::make_smem_desc_hi(C::kSubBytes, 1024);  // V: MN-major
+      auto qk = [&](int t, int stage) {
+        const uint32_t qa = sbase + C::kSmemQ + t * C::kTileBytes;
+        const uint32_t ka = sbase + C::kSmemK + stage * C::kTileBytes;
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+          const uint32_t off = (ks / 4) * C::kSubBytes + (ks % 4) * 32;
+          ptx::mma_ss(tmem + t * 128, ptx::smem_desc(hi_k, qa + off), ptx::smem_desc(hi_k, ka + off),
+                      idesc_qk, ks > 0);
+        }
+      };
+      auto pv = [&](int t, int stage, bool acc) {
+        const uint32_t va = sbase + C::kSmemV + stage * C::kTileBytes;
+#pragma unroll
+        for (int ks = 0; ks < kTileN / 16; ++ks)
+          ptx::mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kPOff + ks * 8,
+                      ptx::smem_desc(hi_mn, va + ks * 2048), idesc_pv, acc || ks > 0);
+      };
+      ptx::mbar_wait(B.q_full, 0);
+      ptx::tc_fence_after();
+      if (nmax > 0) {
+        ptx::mbar_wait(B.k_full, 0);
+        ptx::tc_fence_after();
+        if (ntile[0] > 0) { qk(0, 0); ptx::mma_commit(B.s_full); }
+        if (ntile[1] > 0) { qk(1, 0); ptx::mma_commit(B.s_full + 8); }
+        ptx::mma_commit(B.k_empty);
+      }
+      for (int j = 0; j < nmax; ++j) {
+        const int s = j % C::kStages, sn = (j + 1) % C::kStages;
+        const uint32_t ph = (j / C::kStages) & 1, phn = ((j + 1) / C::kStages) & 1;
+        ptx::mbar_wait(B.v_full + 8 * s, ph);
+        if (j < ntile[0]) {
+          ptx::mbar_wait(B.p_full, j & 1);
+          ptx::tc_fence_after();
+          pv(0, s, j > 0);
+          ptx::mma_commit(B.pv_done);
+        }
+        if (j + 1 < nmax) {
+          ptx::mbar_wait(B.k_full + 8 * sn, phn);
+          ptx::tc_fence_after();
+        }
+        if (j + 1 < ntile[0]) { qk(0, sn); ptx::mma_commit(B.s_full); }
+        if (j < ntile[1]) {
+          ptx::mbar_wait(B.p_full + 8, j & 1);
+          ptx::tc_fence_after();
+          pv(1, s, j > 0);
+          ptx::mma_commit(B.pv_done + 8);
+        }
+        ptx::mma_commit(B.v_empty + 8 * s);
+        if (j + 1 < ntile[1]) { qk(1, sn); ptx::mma_commit(B.s_full + 8); }
+        if (j + 1 < nmax) ptx::mma_commit(B.k_empty + 8 * sn);
+      }
+    }
+  } else {
+    // ======================= softmax warpgroups ===================================
+    ptx::setmaxnreg_inc<232>();
+    const int t = warp >> 2;                          // query tile of this warpgroup
+    const int r_in_tile = (warp & 3) * 32 + lane;     // TMEM lane == row inside the tile
+    const int row = m0 + t * kTileM + r_in_tile;      // row inside the sequence
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem + t * 128 + lane_sel;
+    const uint32_t tP = tS + kPOff;
+    const uint32_t tO = tmem + 256 + t * 128 + lane_sel;
+    const int n_t = ntile[t];
+    const float c2 = a.scale_log2;
+    const int row_limit = row + shift;                // last visible key when causal
+    const int tile_row0 = m0 + t * kTileM;
+
+    DropConst dc;
+    uint32_t bh = 0;
+    if constexpr (kDropout) {
+      dc.add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
+      dc.t_msb = a.drop_threshold >= 128u;
+      bh = (uint32_t)(bidx * a.h + head);
+    }
+
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < n_t; ++j) {
+      ptx::mbar_wait(B.s_full + 8 * t, j & 1);
+      ptx::tc_fence_after();
+      uint32_t s[128];
+      {
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        ptx::tmem_ld_x32(tS, s0);
+        ptx::tmem_ld_x32(tS + 32, s1);
+        ptx::tmem_ld_x32(tS + 64, s2);
+        ptx::tmem_ld_x32(tS + 96, s3);
+        ptx::tmem_wait_ld();
+      }
+      const int col0 = j * kTileN;
+      // masking is needed only on the diagonal and on the ragged last tile (warp-uniform test)
+      const bool need_mask = (col0 + kTileN > sk) || (a.causal && col0 + kTileN - 1 > tile_row0 + shift);
+      if (need_mask) {
+        const int lim = a.causal ? min(sk - 1, row_limit) : sk - 1;
+#pragma unroll
+        for (int c = 0; c < 128; ++c)
+          if (col0 + c > lim) s[c] = 0xff800000u;  // -inf
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 128; c += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(s[c]));
+        mx1 = fmaxf(mx1, __uint_as_float(s[c + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(s[c + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(s[c + 3]));
+      }
+      const float m_new = fmaxf(fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)), m_run);
+      if (j == 0) {
+        m_run = m_new;
+      } else {
+        // lazy rescale: only when some row of this warp grew by more than 2^kRescaleThreshold
+        const bool grow = (m_new - m_run) * c2 > kRescaleThreshold || (m_run == -INFINITY && m_new > m_run);
+        if (__any_sync(0xffffffffu, grow)) {
+          const float alpha = m_new == -INFINITY ? 1.f : exp2f((m_run - m_new) * c2);
+          l_run *= alpha;
+          m_run = m_new;
+          ptx::mbar_wait(B.pv_done + 8 * t, (j - 1) & 1);   // O_t holds tiles 0..j-1
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_x32(tO + c * 32, o);
+            ptx::tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            ptx::tmem_st_x32(tO + c * 32, o);
+          }
+          ptx::tmem_wait_st();
+        }
+      }
+      const float m_use = m_run == -INFINITY ? 0.f : m_run;
+      const float neg_mc = -m_use * c2;
+      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 128; c += 4) {
+        const float p0 = exp2f(fmaf(__uint_as_float(s[c]), c2, neg_mc));
+        const float p1 = exp2f(fmaf(__uint_as_float(s[c + 1]), c2, neg_mc));
+        const float p2 = exp2f(fmaf(__uint_as_float(s[c + 2]), c2, neg_mc));
+        const float p3 = exp2f(fmaf(__uint_as_float(s[c + 3]), c2, neg_mc));
+        l0 += p0; l1 += p1; l2 += p2; l3 += p3;
+        s[c / 2] = pack_pair(p0, p1, kBF16);       // pairs land below the read cursor: c/2 < c
+        s[c / 2 + 1] = pack_pair(p2, p3, kBF16);
+      }
+      l_run += (l0 + l1) + (l2 + l3);
+      if constexpr (kDropout) {
+        // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
+#pragma unroll
+        for (int cb = 0; cb < 8; ++cb) {
+          const fa_philox4_t rnd = fa_philox4x32((uint32_t)row, (uint32_t)(col0 / 16 + cb), bh, a.ctr3,
+                                                 a.key0, a.key1);
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            uint32_t m01, m23;
+            keep_masks(rnd.v[w], dc, m01, m23);
+            s[cb * 8 + w * 2] &= m01;
+            s[cb * 8 + w * 2 + 1] &= m23;
+          }
+        }
+      }
+      {
+        uint32_t(&p0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&p1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        ptx::tmem_st_x32(tP, p0);
+        ptx::tmem_st_x32(tP + 32, p1);
+        ptx::tmem_wait_st();
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.p_full + 8 * t);
+    }
+
+    // ---- epilogue: O_t / l -> global, LSE ------------------------------------------
+    const bool row_ok = row < sq;
+    const size_t tok = (size_t)(a.cu_q ? q0 : bidx * a.sq) + row;
+    uint4 *orow = reinterpret_cast<uint4 *>(static_cast<uint16_t *>(a.out) + (tok * a.h + head) * D);
+    if (n_t > 0) {
+      ptx::mbar_wait(B.pv_done + 8 * t, (n_t - 1) & 1);
+      ptx::tc_fence_after();
+      const float inv = l_run > 0.f ? a.rp_dropout / l_run : 0.f;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        ptx::tmem_ld_x32(tO + c * 32, o);
+        ptx::tmem_wait_ld();
+        if (row_ok) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 v;
+            v.x = pack_pair(__uint_as_float(o[8 * i]) * inv, __uint_as_float(o[8 * i + 1]) * inv, kBF16);
+            v.y = pack_pair(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv, kBF16);
+            v.z = pack_pair(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv, kBF16);
+            v.w = pack_pair(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv, kBF16);
+            orow[c * 4 + i] = v;
+          }
+        }
+      }
+    } else if (row_ok) {
+#pragma unroll
+      for (int i = 0; i < D / 8; ++i) orow[i] = make_uint4(0, 0, 0, 0);
+    }
+    if (row_ok) {
+      const float m_use = m_run == -INFINITY ? 0.f : m_run;
+      a.lse[((size_t)bidx * a.h + head) * a.sq + row] =
+          l_run > 0.f ? (log2f(l_run) + m_use * c2) * kLn2 : INFINITY;
+    }
+  }
+
+  // ---- teardown ----------------------------------------------------------------------
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+}  // namespace

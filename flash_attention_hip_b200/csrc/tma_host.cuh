@@ -1,0 +1,50 @@
+// tma_host.cuh -- host-side TMA tensor-map construction.  cuTensorMapEncodeTiled
+// is fetched through cudaGetDriverEntryPoint so the library links against the
+// runtime only (no -lcuda).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace fa {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// Tensor map over a [tokens, heads, d] 16-bit tensor viewed as 4-D
+// (d, heads, rows, batches): dense layouts pass rows = seqlen, batches = b
+// (out-of-range rows of one sequence then read as zero, never as the next
+// batch entry's data); packed layouts pass rows = total tokens, batches = 1.
+// Box = 64 elements of d (128 bytes, the swizzle span) x 1 head x box_rows rows.
+inline const char *make_tmap_rows(CUtensorMap *m, const void *base, bool is_bf16, int d, int heads,
+                                  uint64_t rows, uint64_t batches, int box_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return "cuTensorMapEncodeTiled is unavailable (driver too old?)";
+  const cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)heads, rows ? rows : 1, batches ? batches : 1};
+  const cuuint64_t strides[3] = {(cuuint64_t)d * 2, (cuuint64_t)heads * d * 2,
+                                 (cuuint64_t)heads * d * 2 * (rows ? rows : 1)};
+  const cuuint32_t box[4] = {64, 1, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                         const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? nullptr : "cuTensorMapEncodeTiled failed";
+}
+
+}  // namespace fa
