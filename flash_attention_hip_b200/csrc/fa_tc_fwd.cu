@@ -74,8 +74,9 @@ struct DropConst {
 __device__ __forceinline__ void keep_masks(uint32_t w, const DropConst &dc, uint32_t &m01, uint32_t &m23) {
   const uint32_t ge7 = (w & 0x7f7f7f7fu) + dc.add7;           // bit7 of each byte: low7 >= T7
   const uint32_t keep = dc.t_msb ? ~(w & ge7) : ~(w | ge7);   // bit7 of each byte: byte < T
-  m01 = __byte_perm(keep, 0, 0x9988);
-  m23 = __byte_perm(keep, 0, 0xbbaa);
+  // prmt's selector bit 3 replicates the byte's sign; __byte_perm() masks it off, hence asm
+  asm("prmt.b32 %0, %1, %1, 0x9988;" : "=r"(m01) : "r"(keep));
+  asm("prmt.b32 %0, %1, %1, 0xbbaa;" : "=r"(m23) : "r"(keep));
 }
 
 }  // namespace
@@ -425,3 +426,69 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 }
 
 }  // namespace
+
+// ---- host side ---------------------------------------------------------------------
+
+bool tc_fwd_supported(const Params &p) {
+  if (p.d != 64 && p.d != 128) return false;
+  if (p.mask || p.softmax_ret) return false;     // bias / S_dmask: all-shapes kernel
+  if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
+  if (p.cu_q) return false;                      // packed layout: not yet on this path
+  if (p.sq <= 0 || p.sk <= 0) return false;
+  return true;
+}
+
+namespace {
+
+template <int D, bool kBF16, bool kDropout>
+const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
+  using C = Cfg<D>;
+  CUtensorMap tq, tk, tv;
+  const bool packed = p.cu_q != nullptr;
+  // dense: (d, heads, seqlen, batch); packed: (d, heads, total tokens, 1)
+  const uint64_t rows_q = packed ? (uint64_t)p.b * p.sq : (uint64_t)p.sq;
+  const uint64_t rows_k = packed ? (uint64_t)p.b * p.sk : (uint64_t)p.sk;
+  const uint64_t nb = packed ? 1 : (uint64_t)p.b;
+  const char *e;
+  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, rows_q, nb, kTileM))) return e;
+  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, rows_k, nb, kTileN))) return e;
+  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, rows_k, nb, kTileN))) return e;
+
+  TcFwdArgs a;
+  a.out = p.out; a.lse = p.lse; a.cu_q = p.cu_q; a.cu_k = p.cu_k;
+  a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk;
+  a.scale_log2 = p.scale * kLog2e;
+  a.rp_dropout = p.rp_dropout;
+  a.drop_threshold = p.drop_threshold;
+  a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
+  a.key1 = (uint32_t)(p.seed >> 32);
+  a.ctr3 = (uint32_t)p.offset;
+  a.causal = p.causal ? 1 : 0;
+
+  auto kern = tc_fwd_kernel<D, kBF16, kDropout>;
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmemBytes) != cudaSuccess)
+      return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+    attr_set = true;
+  }
+  dim3 grid((p.sq + 2 * kTileM - 1) / (2 * kTileM), p.h, p.b);
+  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tq, tk, tv, a);
+  const cudaError_t err = cudaGetLastError();
+  return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
+}
+
+}  // namespace
+
+const char *launch_tc_fwd(const Params &p, cudaStream_t stream) {
+  const bool drop = p.p_dropout > 0.f;
+#define FA_DISPATCH(DD)                                                                        \
+  if (p.is_bf16) return drop ? launch_tc_fwd_t<DD, true, true>(p, stream)                        \
+                             : launch_tc_fwd_t<DD, true, false>(p, stream);                      \
+  return drop ? launch_tc_fwd_t<DD, false, true>(p, stream) : launch_tc_fwd_t<DD, false, false>(p, stream);
+  if (p.d == 128) { FA_DISPATCH(128) }
+  FA_DISPATCH(64)
+#undef FA_DISPATCH
+}
+
+}  // namespace fa
