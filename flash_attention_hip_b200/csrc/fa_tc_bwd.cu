@@ -1,0 +1,572 @@
+// fa_tc_bwd.cu -- FlashAttention-2 backward for sm_100a (tcgen05 + TMEM + TMA).
+// Implements flash_attn_bwd (reference flash_attn.h:68-99) for head_size 64/128.
+//
+// One CTA owns one 128-key tile (K_j, V_j) of one (batch, kv head) and loops over
+// the query tiles that see it (and over the query heads of the GQA group),
+// keeping dK_j and dV_j in tensor memory for the whole loop.  Scores are
+// computed TRANSPOSED, so that TMEM lane == key row and P^T / dS^T are directly
+// the A operands of the dV / dK GEMMs:
+//   (1) S^T  = K_j Q_i^T                  A,B smem K-major        -> TMEM [0,128)
+//   (2) dP^T = V_j dO_i^T                 A,B smem K-major        -> TMEM [128,256)
+//       compute warps: P^T = exp2(S^T c - LSE_i), dS^T = P^T o (dP^T - D_i)
+//   (3) dV_j += P^T dO_i                  A TMEM, B smem MN-major -> TMEM [256,256+D)
+//   (4) dK_j += dS^T Q_i                  A smem K-major (written by threads), B MN-major
+//                                                                 -> TMEM [384,384+D)
+//   (5) dQ_i  = dS K_j                    A smem MN-major (same buffer), B MN-major
+//                                                                 -> TMEM [128,128+D) (reuses dP^T)
+// dQ_i tiles are added into the fp32 scratch `dq_accum` with bulk reduce-adds
+// (cp.reduce.async.bulk .add.f32) of 16 KB blocks; a small kernel converts the
+// scratch to dq.  Sixteen warps:
+//   warps 0-7   compute (lane = key row; warps 0-3 own query columns 0-63, 4-7 own 64-127)
+//   warp  8     tcgen05.mma issue, TMEM alloc/free     warp 9   TMA producer (+ LSE/D staging)
+//   warps 12-15 dQ drain (TMEM -> smem -> bulk reduce-add)
+#include "fa_common.cuh"
+#include "ptx_sm100.cuh"
+#include "tma_host.cuh"
+
+namespace fa {
+
+namespace {
+
+constexpr int kT = 128;            // tile edge: keys per CTA tile, queries per inner tile
+constexpr int kThreads = 512;
+constexpr int kMmaWarp = 8, kLoadWarp = 9, kDrainWarp0 = 12;
+constexpr float kLog2e = 1.4426950408889634f;
+
+template <int D>
+struct Cfg {
+  static constexpr uint32_t kTile = kT * D * 2;       // one 128 x D 16-bit tile
+  static constexpr uint32_t kSub = kT * 128;          // one [128 x 64] swizzled sub-tile
+  static constexpr uint32_t kK = 0;
+  static constexpr uint32_t kV = kK + kTile;
+  static constexpr uint32_t kQ = kV + kTile;          // 2 stages
+  static constexpr uint32_t kDO = kQ + 2 * kTile;
+  static constexpr uint32_t kDS = kDO + kTile;        // dS^T: 128 x 128 16-bit = 32 KB
+  static constexpr uint32_t kDQ = kDS + 2 * kSub;     // 2 x 16 KB fp32 staging blocks
+  static constexpr uint32_t kStat = kDQ + 2 * 16384;  // 2 stages x {lse2[128], D[128]} fp32
+  static constexpr uint32_t kBar = kStat + 2 * 1024;
+  static constexpr uint32_t kNumBars = 16;
+  static constexpr uint32_t kBytes = kBar + kNumBars * 8 + 16;
+};
+
+struct BwdArgs {
+  void *dk, *dv;
+  float *dq_accum;
+  const float *lse, *softmax_d;
+  int b, sq, sk, sq_rounded, h, hk, nqt;
+  float scale, scale_log2, rp_dropout;
+  uint32_t drop_threshold, key0, key1, ctr3;
+  int causal;
+};
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi, bool bf16) {
+  if (bf16) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&v);
+  }
+  const __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t *>(&v);
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+// 16 KB shared -> global, element-wise fp32 add (async proxy, bulk group).
+__device__ __forceinline__ void bulk_reduce_add_f32(float *gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+               ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+}
+
+// 16 keep bits (bit k: byte k of the 4 Philox words < T), csrc/philox_spec.h.
+__device__ __forceinline__ uint32_t keep_bits16(const fa_philox4_t &r, uint32_t add7, bool t_msb) {
+  uint32_t bits = 0;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    const uint32_t x = r.v[w];
+    const uint32_t ge7 = (x & 0x7f7f7f7fu) + add7;
+    const uint32_t keep = (t_msb ? ~(x & ge7) : ~(x | ge7)) & 0x80808080u;
+    // gather bits 7,15,23,31 into a nibble
+    const uint32_t nib = (keep * 0x00204081u) >> 28;
+    bits |= nib << (4 * w);
+  }
+  return bits;
+}
+
+}  // namespace
+
+namespace {
+
+struct BwdBars {
+  uint32_t kv_full, q_full /*[2]*/, q_empty /*[2]*/, do_full, do_empty, s_full, dp_full, p_ready, ds_ready,
+      dq_full, dq_drained, acc_done;
+};
+
+template <int D, bool kBF16, bool kDropout>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
+              const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
+              const BwdArgs a) {
+  using C = Cfg<D>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t sbase = ptx::smem_u32(smem_raw);
+  if (sbase & 1023u) __trap();   // the swizzled tiles need a 1024-byte aligned base
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- problem coordinates ---------------------------------------------------------
+  const int j = blockIdx.x, hk = blockIdx.y, bidx = blockIdx.z;
+  const int sq = a.sq, sk = a.sk;
+  const int group = a.h / a.hk;
+  const int shift = sk - sq;                   // causal: key n visible to row r iff n <= r + shift
+  const int nqt = a.nqt;                       // query tiles of 128 rows
+  int i_min = 0;
+  if (a.causal) {
+    const int first_row = j * kT - shift;      // first query row that sees key j*128
+    i_min = first_row <= 0 ? 0 : first_row / kT;
+  }
+  const int n_i = max(0, nqt - i_min);         // query tiles per head
+  const int n_it = n_i * group;                // inner iterations: (head in group, query tile)
+
+  // ---- barriers, tensor memory --------------------------------------------------------
+  const uint32_t bar0 = sbase + C::kBar;
+  BwdBars B;
+  B.kv_full = bar0;          B.q_full = bar0 + 8;      B.q_empty = bar0 + 24;   B.do_full = bar0 + 40;
+  B.do_empty = bar0 + 48;    B.s_full = bar0 + 56;     B.dp_full = bar0 + 64;   B.p_ready = bar0 + 72;
+  B.ds_ready = bar0 + 80;    B.dq_full = bar0 + 88;    B.dq_drained = bar0 + 96; B.acc_done = bar0 + 104;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem_raw + C::kBar + C::kNumBars * 8);
+
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(B.kv_full, 1);
+    ptx::mbar_init(B.q_full, 2);      ptx::mbar_init(B.q_full + 8, 2);    // TMA expect_tx arrive + stats arrive
+    ptx::mbar_init(B.q_empty, 1);     ptx::mbar_init(B.q_empty + 8, 1);
+    ptx::mbar_init(B.do_full, 1);     ptx::mbar_init(B.do_empty, 1);
+    ptx::mbar_init(B.s_full, 1);      ptx::mbar_init(B.dp_full, 1);
+    ptx::mbar_init(B.p_ready, 256);   ptx::mbar_init(B.ds_ready, 256);
+    ptx::mbar_init(B.dq_full, 1);     ptx::mbar_init(B.dq_drained, 128);
+    ptx::mbar_init(B.acc_done, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == kLoadWarp && lane == 0) {
+    ptx::prefetch_tensormap(&tmap_q);  ptx::prefetch_tensormap(&tmap_k);
+    ptx::prefetch_tensormap(&tmap_v);  ptx::prefetch_tensormap(&tmap_do);
+  }
+  if (warp == kMmaWarp) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 384;
+
+  if (warp >= 8 && warp < 12) {
+    // =========================== producer warpgroup ======================================
+    ptx::setmaxnreg_dec<32>();
+    if (warp == kLoadWarp) {
+      // ---- TMA producer; all 32 lanes stage LSE / D -----------------------------------------
+      if (lane == 0) {
+        ptx::mbar_arrive_expect_tx(B.kv_full, 2 * C::kTile);
+        for (int c = 0; c < D / 64; ++c) {
+          ptx::tma_load_4d(sbase + C::kK + c * C::kSub, &tmap_k, B.kv_full, c * 64, hk, j * kT, bidx);
+          ptx::tma_load_4d(sbase + C::kV + c * C::kSub, &tmap_v, B.kv_full, c * 64, hk, j * kT, bidx);
+        }
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+        const int s = it & 1;
+        if (it >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((it >> 1) - 1) & 1);
+        if (lane == 0) {
+          ptx::mbar_arrive_expect_tx(B.q_full + 8 * s, C::kTile);
+          for (int c = 0; c < D / 64; ++c)
+            ptx::tma_load_4d(sbase + C::kQ + s * C::kTile + c * C::kSub, &tmap_q, B.q_full + 8 * s,
+                             c * 64, hq, i * kT, bidx);
+        }
+        {
+          // lse2 = LSE * log2(e) (+inf past the sequence end => P = 0 there), D = rowsum(dO o O)
+          const float *lse = a.lse + ((size_t)bidx * a.h + hq) * sq;
+          const float *dd = a.softmax_d + ((size_t)bidx * a.h + hq) * a.sq_rounded;
+          const uint32_t st = sbase + C::kStat + s * 1024;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int r = t * 32 + lane, row = i * kT + r;
+            const float l = row < sq ? lse[row] : INFINITY;
+            const float dv = row < sq ? dd[row] : 0.f;
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 4 * r), "f"(l * kLog2e) : "memory");
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 512 + 4 * r), "f"(dv) : "memory");
+          }
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(B.q_full + 8 * s);
+        }
+        if (it >= 1) ptx::mbar_wait(B.do_empty, (it - 1) & 1);
+        if (lane == 0) {
+          ptx::mbar_arrive_expect_tx(B.do_full, C::kTile);
+          for (int c = 0; c < D / 64; ++c)
+            ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, &tmap_do, B.do_full, c * 64, hq, i * kT, bidx);
+        }
+      }
+    } else if (warp == kMmaWarp && lane == 0) {
+      // ---- MMA issuer -----------------------------------------------------------------------
+      constexpr uint32_t fmt = kBF16 ? ptx::kFmtBF16 : ptx::kFmtF16;
+      constexpr uint32_t id_kk = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorK, kT, kT);     // (1) (2)
+      constexpr uint32_t id_k_mn = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorMN, kT, D);   // (3) (4)
+      constexpr uint32_t id_mn_mn = ptx::make_idesc(fmt, ptx::kMajorMN, ptx::kMajorMN, kT, D); // (5)
+      constexpr uint64_t hi_k = ptx::make_smem_desc_hi(16, 1024);
+      constexpr uint64_t hi_mn = ptx::make_smem_desc_hi(C::kSub, 1024);
+      // D(tmem) = A(K-major smem) * B(K-major smem), contraction over d
+      auto gemm_kk = [&](uint32_t d_tmem, uint32_t a_smem, uint32_t b_smem) {
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+          const uint32_t off = (ks / 4) * C::kSub + (ks % 4) * 32;
+          ptx::mma_ss(d_tmem, ptx::smem_desc(hi_k, a_smem + off), ptx::smem_desc(hi_k, b_smem + off), id_kk, ks > 0);
+        }
+      };
+      ptx::mbar_wait(B.kv_full, 0);
+      ptx::tc_fence_after();
+      if (n_it > 0) {
+        ptx::mbar_wait(B.q_full, 0);
+        ptx::tc_fence_after();
+        gemm_kk(tS, sbase + C::kK, sbase + C::kQ);                       // (1) S^T(0)
+        ptx::mma_commit(B.s_full);
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int s = it & 1;
+        const uint32_t qa = sbase + C::kQ + s * C::kTile;
+        ptx::mbar_wait(B.do_full, it & 1);
+        if (it > 0) ptx::mbar_wait(B.dq_drained, (it - 1) & 1);           // dP^T shares TMEM with dQ
+        ptx::tc_fence_after();
+        gemm_kk(tDP, sbase + C::kV, sbase + C::kDO);                      // (2) dP^T(it)
+        ptx::mma_commit(B.dp_full);
+        ptx::mbar_wait(B.p_ready, it & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int ks = 0; ks < kT / 16; ++ks)                               // (3) dV += P^T dO
+          ptx::mma_ts(tDV, tS + (ks / 4) * 64 + (ks % 4) * 8,
+                      ptx::smem_desc(hi_mn, sbase + C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
+        ptx::mma_commit(B.do_empty);
+        if (it + 1 < n_it) {
+          ptx::mbar_wait(B.q_full + 8 * (s ^ 1), ((it + 1) >> 1) & 1);
+          ptx::tc_fence_after();
+          gemm_kk(tS, sbase + C::kK, sbase + C::kQ + (s ^ 1) * C::kTile);  // (1) S^T(it+1)
+          ptx::mma_commit(B.s_full);
+        }
+        ptx::mbar_wait(B.ds_ready, it & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int ks = 0; ks < kT / 16; ++ks) {                             // (4) dK += dS^T Q
+          const uint32_t aoff = (ks / 4) * C::kSub + (ks % 4) * 32;
+          ptx::mma_ss(tDK, ptx::smem_desc(hi_k, sbase + C::kDS + aoff), ptx::smem_desc(hi_mn, qa + ks * 2048),
+                      id_k_mn, it > 0 || ks > 0);
+        }
+        ptx::mma_commit(B.q_empty + 8 * s);
+#pragma unroll
+        for (int ks = 0; ks < kT / 16; ++ks)                               // (5) dQ = dS K
+          ptx::mma_ss(tDP, ptx::smem_desc(hi_mn, sbase + C::kDS + ks * 2048),
+                      ptx::smem_desc(hi_mn, sbase + C::kK + ks * 2048), id_mn_mn, ks > 0);
+        ptx::mma_commit(B.dq_full);
+      }
+      ptx::mma_commit(B.acc_done);
+    }
+  } else if (warp >= kDrainWarp0) {
+    // =========================== dQ drain warpgroup ======================================
+    ptx::setmaxnreg_dec<80>();
+    const int dw = warp - kDrainWarp0;                 // == warp % 4: TMEM lane quadrant
+    const int r = dw * 32 + lane;                      // query row inside the tile == TMEM lane
+    const uint32_t lane_sel = (uint32_t)(dw * 32) << 16;
+    const bool leader = (warp == kDrainWarp0 && lane == 0);
+    uint32_t cc = 0;                                   // running 16 KB block counter (staging ring of 2)
+    for (int it = 0; it < n_it; ++it) {
+      const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+      // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
+      float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * nqt + i) * (D / 32)) * 4096;
+      ptx::mbar_wait(B.dq_full, it & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c, ++cc) {
+        uint32_t v[32];
+        ptx::tmem_ld_x32(tDP + lane_sel + c * 32, v);
+        ptx::tmem_wait_ld();
+        if (c == D / 32 - 1) {                         // TMEM tile fully read: dP^T(it+1) may overwrite it
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(B.dq_drained);
+        }
+        const uint32_t buf = sbase + C::kDQ + (cc & 1) * 16384;
+        if (leader && cc >= 2) ptx::tma_store_wait_read<1>();   // the block that used `buf` has been read
+        ptx::named_bar_sync(1, 128);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          st_shared_v4(buf + r * 128 + ((k ^ (r & 7)) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        ptx::fence_proxy_async_smem();
+        ptx::named_bar_sync(1, 128);
+        if (leader) {
+          bulk_reduce_add_f32(gdst + c * 4096, buf, 16384);
+          ptx::tma_store_commit();
+        }
+      }
+    }
+    if (leader) ptx::tma_store_wait<0>();
+  } else {
+    // =========================== compute warps ============================================
+    ptx::setmaxnreg_inc<200>();
+    const int w = warp >> 2;                           // which 64 query columns
+    const int n = (warp & 3) * 32 + lane;              // key row inside the tile == TMEM lane
+    const int n_abs = j * kT + n;
+    const bool kv_valid = n_abs < sk;
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    const float c2 = a.scale_log2;
+    uint32_t add7 = 0;
+    bool t_msb = false;
+    if constexpr (kDropout) {
+      add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
+      t_msb = a.drop_threshold >= 128u;
+    }
+
+    for (int it = 0; it < n_it; ++it) {
+      const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+      const int s = it & 1;
+      const uint32_t stat = sbase + C::kStat + s * 1024 + w * 256;   // lse2 / D of my 64 query columns
+      const int q_base = i * kT + w * 64;
+
+      // dropout keep bits for my 64 (query, key) pairs: lanes of a half-warp share the key
+      // block, so each lane draws the 16 bytes of ONE query row and the rows are exchanged.
+      uint32_t keep_lo = 0xffffffffu, keep_hi = 0xffffffffu;
+      if constexpr (kDropout) {
+        keep_lo = keep_hi = 0;
+        const uint32_t bh = (uint32_t)(bidx * a.h + hq);
+#pragma unroll
+        for (int blk = 0; blk < 4; ++blk) {
+          const fa_philox4_t rnd = fa_philox4x32((uint32_t)(q_base + blk * 16 + (lane & 15)),
+                                                 (uint32_t)(n_abs >> 4), bh, a.ctr3, a.key0, a.key1);
+          const uint32_t mine = keep_bits16(rnd, add7, t_msb);
+          uint32_t bits = 0;
+#pragma unroll
+          for (int t = 0; t < 16; ++t) {
+            const uint32_t m = __shfl_sync(0xffffffffu, mine, (lane & 16) | t);
+            bits |= ((m >> (lane & 15)) & 1u) << t;
+          }
+          if (blk < 2) keep_lo |= bits << (16 * blk);
+          else keep_hi |= bits << (16 * (blk - 2));
+        }
+      }
+
+      ptx::mbar_wait(B.q_full + 8 * s, (it >> 1) & 1);   // LSE / D staged
+      ptx::mbar_wait(B.s_full, it & 1);
+      ptx::tc_fence_after();
+      float p[64];
+      {
+        uint32_t(&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&p[0]);
+        uint32_t(&r1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&p[32]);
+        ptx::tmem_ld_x32(tS + lane_sel + w * 64, r0);
+        ptx::tmem_ld_x32(tS + lane_sel + w * 64 + 32, r1);
+        ptx::tmem_wait_ld();
+      }
+      const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
+      const int lim = n_abs - shift;                     // causal: visible iff q >= lim
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        const float lse2 = ld_shared_f32(stat + 4 * c);
+        float e = exp2f(fmaf(p[c], c2, -lse2));
+        if (!kv_valid || (diag && q_base + c < lim)) e = 0.f;
+        p[c] = e;
+      }
+      {
+        uint32_t pk[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          float lo = p[2 * c], hi = p[2 * c + 1];
+          if constexpr (kDropout) {
+            const uint32_t kb = c < 16 ? keep_lo >> (2 * c) : keep_hi >> (2 * c - 32);
+            if (!(kb & 1u)) lo = 0.f;
+            if (!(kb & 2u)) hi = 0.f;
+          }
+          pk[c] = pack2(lo, hi, kBF16);
+        }
+        ptx::tmem_st_x32(tS + lane_sel + w * 64, pk);     // P^T half w lives in columns [64w, 64w+32)
+        ptx::tmem_wait_st();
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.p_ready);
+
+      ptx::mbar_wait(B.dp_full, it & 1);
+      ptx::tc_fence_after();
+      uint32_t ds[32];
+      {
+        uint32_t dp[32];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          ptx::tmem_ld_x32(tDP + lane_sel + w * 64 + half * 32, dp);
+          ptx::tmem_wait_ld();
+#pragma unroll
+          for (int c = 0; c < 32; c += 2) {
+            const int cq = half * 32 + c;
+            float g0 = __uint_as_float(dp[c]), g1 = __uint_as_float(dp[c + 1]);
+            if constexpr (kDropout) {
+              const uint32_t kb = cq < 32 ? keep_lo >> cq : keep_hi >> (cq - 32);
+              g0 = (kb & 1u) ? g0 * a.rp_dropout : 0.f;
+              g1 = (kb & 2u) ? g1 * a.rp_dropout : 0.f;
+            }
+            const float d0 = ld_shared_f32(stat + 512 + 4 * cq), d1 = ld_shared_f32(stat + 512 + 4 * cq + 4);
+            ds[cq / 2] = pack2(p[cq] * (g0 - d0), p[cq + 1] * (g1 - d1), kBF16);
+          }
+        }
+      }
+      if (it > 0) ptx::mbar_wait(B.dq_full, (it - 1) & 1);   // GEMMs (4),(5) of it-1 have read dS^T
+      {
+        const uint32_t rowp = sbase + C::kDS + w * C::kSub + n * 128;
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          st_shared_v4(rowp + ((k ^ (n & 7)) << 4), ds[4 * k], ds[4 * k + 1], ds[4 * k + 2], ds[4 * k + 3]);
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.ds_ready);
+    }
+
+    // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
+    ptx::mbar_wait(B.acc_done, 0);
+    ptx::tc_fence_after();
+    constexpr int kHalf = D / 2;                         // columns per warp half
+    const size_t tok = (size_t)bidx * sk + n_abs;
+    uint16_t *dkp = static_cast<uint16_t *>(a.dk) + (tok * a.hk + hk) * D + w * kHalf;
+    uint16_t *dvp = static_cast<uint16_t *>(a.dv) + (tok * a.hk + hk) * D + w * kHalf;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      const uint32_t tsrc = (which ? tDK : tDV) + lane_sel + w * kHalf;
+      const float mul = n_it == 0 ? 0.f : (which ? a.scale : a.rp_dropout);
+      uint4 *dst = reinterpret_cast<uint4 *>(which ? dkp : dvp);
+#pragma unroll
+      for (int c = 0; c < kHalf / 32; ++c) {
+        uint32_t v[32];
+        if (n_it > 0) {
+          ptx::tmem_ld_x32(tsrc + c * 32, v);
+          ptx::tmem_wait_ld();
+        } else {
+#pragma unroll
+          for (int x = 0; x < 32; ++x) v[x] = 0;
+        }
+        if (kv_valid) {
+#pragma unroll
+          for (int x = 0; x < 4; ++x) {
+            uint4 o;
+            o.x = pack2(__uint_as_float(v[8 * x]) * mul, __uint_as_float(v[8 * x + 1]) * mul, kBF16);
+            o.y = pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16);
+            o.z = pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16);
+            o.w = pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16);
+            dst[c * 4 + x] = o;
+          }
+        }
+      }
+    }
+  }
+
+  // ---- teardown -------------------------------------------------------------------------------
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// dq = softmax_scale * dq_accum, un-swizzling the [tile][D/32][128][32] scratch layout.
+template <int D, bool kBF16>
+__global__ void __launch_bounds__(256)
+dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, int sq, int h, int nqt, float scale) {
+  const int i = blockIdx.x, hq = blockIdx.y, bidx = blockIdx.z;
+  const float *src = acc + ((((size_t)bidx * h + hq) * nqt + i) * (D / 32)) * 4096;
+  constexpr int kVecPerRow = D / 8;                    // 16-byte output vectors per row
+  for (int idx = threadIdx.x; idx < 128 * kVecPerRow; idx += 256) {
+    const int r = idx / kVecPerRow, vcol = idx % kVecPerRow;
+    const int row = i * 128 + r;
+    if (row >= sq) continue;
+    const int d0 = vcol * 8, c = d0 / 32, k = (d0 % 32) / 4;       // two 16-byte chunks k, k+1
+    const float *rowp = src + (size_t)c * 4096 + r * 32;
+    const float4 x = *reinterpret_cast<const float4 *>(rowp + ((k ^ (r & 7)) << 2));
+    const float4 y = *reinterpret_cast<const float4 *>(rowp + (((k + 1) ^ (r & 7)) << 2));
+    uint4 o;
+    o.x = pack2(x.x * scale, x.y * scale, kBF16);
+    o.y = pack2(x.z * scale, x.w * scale, kBF16);
+    o.z = pack2(y.x * scale, y.y * scale, kBF16);
+    o.w = pack2(y.z * scale, y.w * scale, kBF16);
+    uint16_t *dst = static_cast<uint16_t *>(dq) + (((size_t)bidx * sq + row) * h + hq) * D + d0;
+    *reinterpret_cast<uint4 *>(dst) = o;
+  }
+}
+
+template <int D, bool kBF16, bool kDropout>
+const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
+  using C = Cfg<D>;
+  CUtensorMap tq, tk, tv, tdo;
+  const char *e;
+  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, p.sq, p.b, kT))) return e;
+  if ((e = make_tmap_rows(&tdo, p.dout, kBF16, D, p.h, p.sq, p.b, kT))) return e;
+  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, p.sk, p.b, kT))) return e;
+  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, p.sk, p.b, kT))) return e;
+
+  BwdArgs a;
+  a.dk = p.dk; a.dv = p.dv; a.dq_accum = p.dq_accum; a.lse = p.lse; a.softmax_d = p.softmax_d;
+  a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.sq_rounded = p.sq_rounded; a.h = p.h; a.hk = p.hk;
+  a.nqt = (p.sq + kT - 1) / kT;
+  a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
+  a.drop_threshold = p.drop_threshold;
+  a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
+  a.key1 = (uint32_t)(p.seed >> 32);
+  a.ctr3 = (uint32_t)p.offset;
+  a.causal = p.causal ? 1 : 0;
+
+  const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * D * sizeof(float);
+  if (cudaMemsetAsync(p.dq_accum, 0, acc_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq_accum) failed";
+
+  auto kern = tc_bwd_kernel<D, kBF16, kDropout>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kBytes) != cudaSuccess)
+      return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+    attr_set = true;
+  }
+  dim3 grid((p.sk + kT - 1) / kT, p.hk, p.b);
+  kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, a);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) return cudaGetErrorString(err);
+  dim3 cgrid(a.nqt, p.h, p.b);
+  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.sq, p.h, a.nqt, p.scale);
+  err = cudaGetLastError();
+  return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
+}
+
+}  // namespace
+
+bool tc_bwd_supported(const Params &p) {
+  if (p.d != 64 && p.d != 128) return false;
+  if (p.mask || p.cu_q) return false;
+  if (!(p.scale > 0.f)) return false;
+  if (p.sq <= 0 || p.sk <= 0) return false;
+  if (p.deterministic) return false;                  // reduce-add order is not fixed
+  if (!p.dq_accum) return false;
+  // scratch contract (include/flash_attn.h): dq_accum >= b * sq_rounded * h * d_rounded floats
+  if (p.sq_rounded % kT || p.sq_rounded < p.sq || p.d_rounded < p.d) return false;
+  return true;
+}
+
+const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
+  const bool drop = p.p_dropout > 0.f;
+#define FA_DISPATCH(DD)                                                                          \
+  if (p.is_bf16) return drop ? launch_tc_bwd_t<DD, true, true>(p, stream)                          \
+                             : launch_tc_bwd_t<DD, true, false>(p, stream);                        \
+  return drop ? launch_tc_bwd_t<DD, false, true>(p, stream) : launch_tc_bwd_t<DD, false, false>(p, stream);
+  if (p.d == 128) { FA_DISPATCH(128) }
+  FA_DISPATCH(64)
+#undef FA_DISPATCH
+}
+
+}  // namespace fa

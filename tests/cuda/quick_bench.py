@@ -27,3 +27,35 @@ if __name__ == "__main__":
     time_fwd(16, 4096, 32, 128, False)
     time_fwd(4, 8192, 16, 128, False)
     time_fwd(16, 4096, 32, 64, True)
+
+
+def time_bwd(b, s, h, d, causal, p=0.0, iters=10, dtype=torch.bfloat16, hk=None):
+    hk = hk or h
+    q = torch.randn(b, s, h, d, device="cuda", dtype=dtype)
+    k = torch.randn(b, s, hk, d, device="cuda", dtype=dtype); v = torch.randn_like(k)
+    do = torch.randn_like(q)
+    out, lse, _, _ = api.flash_attn_fwd(q, k, v, is_causal=causal, p_dropout=p)
+    sq_r, d_r = api.round_up(s, 128), api.round_up(d, 32)
+    scratch = (torch.empty((b, h, sq_r), dtype=torch.float32, device="cuda"),
+               torch.empty((b, sq_r, h, d_r), dtype=torch.float32, device="cuda"))
+    grads = (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
+    for _ in range(2):
+        api.flash_attn_bwd(do, q, k, v, out, lse, is_causal=causal, p_dropout=p, scratch=scratch, grads=grads)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        api.flash_attn_bwd(do, q, k, v, out, lse, is_causal=causal, p_dropout=p, scratch=scratch, grads=grads)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    fl = 2.5 * 4.0 * b * h * s * s * d * (0.5 if causal else 1.0)
+    print(f"bwd b{b} s{s} h{h}/{hk} d{d} causal={causal} p={p} path={api.last_path()}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
+
+
+if __name__ == "__main__":
+    time_bwd(8, 2048, 16, 128, True)
+    time_bwd(16, 4096, 32, 128, True)
+    time_bwd(16, 4096, 32, 128, True, p=0.1)
+    time_bwd(16, 4096, 32, 128, False)
+    time_bwd(16, 4096, 32, 64, True)
+    time_bwd(4, 8192, 32, 128, True, hk=8)
