@@ -46,14 +46,19 @@ struct Cfg {
   static constexpr uint32_t kStat = kDQ + 2 * 16384;  // 2 stages x {lse2[128], D[128]} fp32
   static constexpr uint32_t kBar = kStat + 2 * 1024;
   static constexpr uint32_t kNumBars = 16;
-  static constexpr uint32_t kBytes = kBar + kNumBars * 8 + 16;
+  static constexpr uint32_t kDesc = kBar + 256;        // 4 x 128 B tensor-map staging (packed inputs)
+  static constexpr uint32_t kBytes = kDesc + 4 * 128;
+  static_assert(kBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
+
+__device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][4];
 
 struct BwdArgs {
   void *dk, *dv;
   float *dq_accum;
   const float *lse, *softmax_d;
-  int b, sq, sk, sq_rounded, h, hk, nqt;
+  const int32_t *cu_q, *cu_k;
+  int b, sq, sk, sq_rounded, h, hk, nqt;   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
@@ -121,10 +126,17 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
   // ---- problem coordinates ---------------------------------------------------------
   const int j = blockIdx.x, hk = blockIdx.y, bidx = blockIdx.z;
-  const int sq = a.sq, sk = a.sk;
+  int sq = a.sq, sk = a.sk, qrow0 = 0, krow0 = 0, bcoord = bidx;   // TMA row origin / batch coordinate
+  size_t qtok0 = (size_t)bidx * a.sq, ktok0 = (size_t)bidx * a.sk; // first token of this sequence
+  if (a.cu_q) {
+    qrow0 = a.cu_q[bidx]; krow0 = a.cu_k[bidx];
+    sq = a.cu_q[bidx + 1] - qrow0; sk = a.cu_k[bidx + 1] - krow0;
+    qtok0 = (size_t)qrow0; ktok0 = (size_t)krow0; bcoord = 0;
+  }
+  if (j * kT >= sk) return;                    // packed: this sequence has no such key tile
   const int group = a.h / a.hk;
   const int shift = sk - sq;                   // causal: key n visible to row r iff n <= r + shift
-  const int nqt = a.nqt;                       // query tiles of 128 rows
+  const int nqt = (sq + kT - 1) / kT;          // query tiles of this sequence
   int i_min = 0;
   if (a.causal) {
     const int first_row = j * kT - shift;      // first query row that sees key j*128
@@ -171,11 +183,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::setmaxnreg_dec<32>();
     if (warp == kLoadWarp) {
       // ---- TMA producer; all 32 lanes stage LSE / D -----------------------------------------
+      const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v, *mdo = &tmap_do;
+      if (a.cu_q) {
+        // packed inputs: rows past this sequence's end must read as zero, not as the next sequence
+        const uint32_t sm = ptx::smid();
+        if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+        const uint32_t d0 = sbase + C::kDesc;
+        uint8_t *g0 = smem_raw + C::kDesc;
+        mq = ptx::patch_rows(tmap_q, &g_bwd_slots[sm][0], d0, g0, (uint32_t)(qrow0 + sq), lane);
+        mdo = ptx::patch_rows(tmap_do, &g_bwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(qrow0 + sq), lane);
+        mk = ptx::patch_rows(tmap_k, &g_bwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(krow0 + sk), lane);
+        mv = ptx::patch_rows(tmap_v, &g_bwd_slots[sm][3], d0 + 384, g0 + 384, (uint32_t)(krow0 + sk), lane);
+      }
       if (lane == 0) {
         ptx::mbar_arrive_expect_tx(B.kv_full, 2 * C::kTile);
         for (int c = 0; c < D / 64; ++c) {
-          ptx::tma_load_4d(sbase + C::kK + c * C::kSub, &tmap_k, B.kv_full, c * 64, hk, j * kT, bidx);
-          ptx::tma_load_4d(sbase + C::kV + c * C::kSub, &tmap_v, B.kv_full, c * 64, hk, j * kT, bidx);
+          ptx::tma_load_4d(sbase + C::kK + c * C::kSub, mk, B.kv_full, c * 64, hk, krow0 + j * kT, bcoord);
+          ptx::tma_load_4d(sbase + C::kV + c * C::kSub, mv, B.kv_full, c * 64, hk, krow0 + j * kT, bcoord);
         }
       }
       for (int it = 0; it < n_it; ++it) {
@@ -185,12 +209,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.q_full + 8 * s, C::kTile);
           for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kQ + s * C::kTile + c * C::kSub, &tmap_q, B.q_full + 8 * s,
-                             c * 64, hq, i * kT, bidx);
+            ptx::tma_load_4d(sbase + C::kQ + s * C::kTile + c * C::kSub, mq, B.q_full + 8 * s,
+                             c * 64, hq, qrow0 + i * kT, bcoord);
         }
         {
           // lse2 = LSE * log2(e) (+inf past the sequence end => P = 0 there), D = rowsum(dO o O)
-          const float *lse = a.lse + ((size_t)bidx * a.h + hq) * sq;
+          const float *lse = a.lse + ((size_t)bidx * a.h + hq) * a.sq;
           const float *dd = a.softmax_d + ((size_t)bidx * a.h + hq) * a.sq_rounded;
           const uint32_t st = sbase + C::kStat + s * 1024;
 #pragma unroll
@@ -208,7 +232,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.do_full, C::kTile);
           for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, &tmap_do, B.do_full, c * 64, hq, i * kT, bidx);
+            ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, mdo, B.do_full, c * 64, hq, qrow0 + i * kT, bcoord);
         }
       }
     } else if (warp == kMmaWarp && lane == 0) {
@@ -284,7 +308,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = i_min + it % n_i;
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
-      float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * nqt + i) * (D / 32)) * 4096;
+      float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * (D / 32)) * 4096;
       ptx::mbar_wait(B.dq_full, it & 1);
       ptx::tc_fence_after();
 #pragma unroll
@@ -432,7 +456,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::mbar_wait(B.acc_done, 0);
     ptx::tc_fence_after();
     constexpr int kHalf = D / 2;                         // columns per warp half
-    const size_t tok = (size_t)bidx * sk + n_abs;
+    const size_t tok = ktok0 + n_abs;
     uint16_t *dkp = static_cast<uint16_t *>(a.dk) + (tok * a.hk + hk) * D + w * kHalf;
     uint16_t *dvp = static_cast<uint16_t *>(a.dv) + (tok * a.hk + hk) * D + w * kHalf;
 #pragma unroll
@@ -481,8 +505,15 @@ namespace {
 // dq = softmax_scale * dq_accum, un-swizzling the [tile][D/32][128][32] scratch layout.
 template <int D, bool kBF16>
 __global__ void __launch_bounds__(256)
-dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, int sq, int h, int nqt, float scale) {
+dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const int32_t *__restrict__ cu_q,
+                  int sq, int h, int nqt, float scale) {
   const int i = blockIdx.x, hq = blockIdx.y, bidx = blockIdx.z;
+  size_t tok0 = (size_t)bidx * sq;
+  if (cu_q) {
+    tok0 = (size_t)cu_q[bidx];
+    sq = cu_q[bidx + 1] - cu_q[bidx];
+    if (i * 128 >= sq) return;
+  }
   const float *src = acc + ((((size_t)bidx * h + hq) * nqt + i) * (D / 32)) * 4096;
   constexpr int kVecPerRow = D / 8;                    // 16-byte output vectors per row
   for (int idx = threadIdx.x; idx < 128 * kVecPerRow; idx += 256) {
@@ -498,7 +529,7 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, int sq, 
     o.y = pack2(x.z * scale, x.w * scale, kBF16);
     o.z = pack2(y.x * scale, y.y * scale, kBF16);
     o.w = pack2(y.z * scale, y.w * scale, kBF16);
-    uint16_t *dst = static_cast<uint16_t *>(dq) + (((size_t)bidx * sq + row) * h + hq) * D + d0;
+    uint16_t *dst = static_cast<uint16_t *>(dq) + ((tok0 + row) * h + hq) * D + d0;
     *reinterpret_cast<uint4 *>(dst) = o;
   }
 }
@@ -508,13 +539,16 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
   CUtensorMap tq, tk, tv, tdo;
   const char *e;
-  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, p.sq, p.b, kT))) return e;
-  if ((e = make_tmap_rows(&tdo, p.dout, kBF16, D, p.h, p.sq, p.b, kT))) return e;
-  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, p.sk, p.b, kT))) return e;
-  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, p.sk, p.b, kT))) return e;
+  // packed: one batch entry whose row count each CTA replaces (ptx::patch_rows)
+  const uint64_t nb = p.cu_q ? 1 : (uint64_t)p.b;
+  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, p.sq, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tdo, p.dout, kBF16, D, p.h, p.sq, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, p.sk, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, p.sk, nb, kT))) return e;
 
   BwdArgs a;
   a.dk = p.dk; a.dv = p.dv; a.dq_accum = p.dq_accum; a.lse = p.lse; a.softmax_d = p.softmax_d;
+  a.cu_q = p.cu_q; a.cu_k = p.cu_k;
   a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.sq_rounded = p.sq_rounded; a.h = p.h; a.hk = p.hk;
   a.nqt = (p.sq + kT - 1) / kT;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
@@ -539,7 +573,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
-  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.sq, p.h, a.nqt, p.scale);
+  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale);
   err = cudaGetLastError();
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
 }
@@ -548,7 +582,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d != 64 && p.d != 128) return false;
-  if (p.mask || p.cu_q) return false;
+  if (p.mask) return false;
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
   if (p.deterministic) return false;                  // reduce-add order is not fixed

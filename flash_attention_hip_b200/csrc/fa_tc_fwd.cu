@@ -47,8 +47,14 @@ struct Cfg {
   static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
   static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
   static constexpr uint32_t kNumBars = 1 + 4 * kStages + 6;
-  static constexpr uint32_t kSmemBytes = kSmemBar + kNumBars * 8 + 16 + 1024;  // + alignment slack
+  static constexpr uint32_t kSmemDesc = kSmemBar + 256;       // 3 x 128 B tensor-map staging (packed inputs)
+  static constexpr uint32_t kSmemBytes = kSmemDesc + 3 * 128 + 1024;  // + alignment slack
+  static_assert(kNumBars * 8 + 16 <= 256, "barrier block overflows");
+  static_assert(kSmemBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
+
+// Per-SM homes of the tensor maps a CTA bounds to its own sequence (packed inputs only).
+__device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][3];
 
 struct Bars {
   uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_full, pv_done;  // first of each group
@@ -178,6 +184,17 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   if (warp >= 8) {
     // ======================= producer warpgroup ================================
     ptx::setmaxnreg_dec<40>();
+    const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v;
+    if (warp == kLoadWarp && a.cu_q) {
+      // packed inputs: rows past this sequence's end must read as zero, not as the next sequence
+      const uint32_t sm = ptx::smid();
+      if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+      const uint32_t d0 = sbase + C::kSmemDesc;
+      uint8_t *g0 = sgen + C::kSmemDesc;
+      mq = ptx::patch_rows(tmap_q, &g_fwd_slots[sm][0], d0, g0, (uint32_t)(q0 + sq), lane);
+      mk = ptx::patch_rows(tmap_k, &g_fwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(k0 + sk), lane);
+      mv = ptx::patch_rows(tmap_v, &g_fwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(k0 + sk), lane);
+    }
     if (warp == kLoadWarp && lane == 0) {
       // ---- TMA producer --------------------------------------------------------
       const int qrow = q0 * (a.cu_q ? 1 : 0) + m0;   // packed: absolute token row; dense: row in sequence
@@ -185,7 +202,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::mbar_arrive_expect_tx(B.q_full, (has_tile1 ? 2 : 1) * C::kTileBytes);
       for (int t = 0; t < (has_tile1 ? 2 : 1); ++t)
         for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, &tmap_q, B.q_full,
+          ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, mq, B.q_full,
                            c * 64, head, qrow + t * kTileM, bcoord);
       for (int j = 0; j < nmax; ++j) {
         const int s = j % C::kStages;
@@ -193,12 +210,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (j >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
         ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
         for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, &tmap_k,
+          ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, mk,
                            B.k_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
         if (j >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
         ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
         for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, &tmap_v,
+          ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, mv,
                            B.v_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
       }
     } else if (warp == kMmaWarp && lane == 0) {
@@ -433,7 +450,6 @@ bool tc_fwd_supported(const Params &p) {
   if (p.d != 64 && p.d != 128) return false;
   if (p.mask || p.softmax_ret) return false;     // bias / S_dmask: all-shapes kernel
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
-  if (p.cu_q) return false;                      // packed layout: not yet on this path
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;
 }
@@ -446,8 +462,8 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   CUtensorMap tq, tk, tv;
   const bool packed = p.cu_q != nullptr;
   // dense: (d, heads, seqlen, batch); packed: (d, heads, total tokens, 1)
-  const uint64_t rows_q = packed ? (uint64_t)p.b * p.sq : (uint64_t)p.sq;
-  const uint64_t rows_k = packed ? (uint64_t)p.b * p.sk : (uint64_t)p.sk;
+  // packed: the row count is a placeholder; each CTA bounds its copy of the map (ptx::patch_rows)
+  const uint64_t rows_q = (uint64_t)p.sq, rows_k = (uint64_t)p.sk;
   const uint64_t nb = packed ? 1 : (uint64_t)p.b;
   const char *e;
   if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, rows_q, nb, kTileM))) return e;

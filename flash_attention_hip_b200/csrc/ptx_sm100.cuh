@@ -213,6 +213,58 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+
+// ---------------------------------------------- device-side tensor-map patching
+// Packed (varlen) inputs: the host cannot know a sequence's last row (cu_seqlens
+// lives on the device), so each CTA bounds its own copy of the tensor map:
+// copy the 128-byte map to shared memory, replace one global dimension, publish
+// it to a global slot with tensormap.cp_fenceproxy, acquire it for the TMA unit.
+
+__device__ __forceinline__ void tensormap_replace_dim2_smem(uint32_t smem_desc, uint32_t new_dim) {
+  asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 2, %1;" ::"r"(smem_desc),
+               "r"(new_dim)
+               : "memory");
+}
+
+// Whole warp (.sync.aligned): shared-memory copy -> global slot, release at gpu scope.
+__device__ __forceinline__ void tensormap_publish(const void *gmem_slot, uint32_t smem_desc) {
+  asm volatile(
+      "tensormap.cp_fenceproxy.global.shared::cta.tensormap::generic.release.gpu.sync.aligned [%0], [%1], 128;"
+      ::"l"(reinterpret_cast<uint64_t>(gmem_slot)), "r"(smem_desc)
+      : "memory");
+}
+
+__device__ __forceinline__ void tensormap_acquire(const void *gmem_slot) {
+  asm volatile("fence.proxy.tensormap::generic.acquire.gpu [%0], 128;" ::"l"(reinterpret_cast<uint64_t>(gmem_slot))
+               : "memory");
+}
+
+__device__ __forceinline__ uint32_t smid() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+  return r;
+}
+
+// Per-SM slots for patched tensor maps.  Every kernel that uses them needs more
+// than half of an SM's shared memory, so at most one such CTA is resident per
+// SM and slot [smid] has a single owner at any time.
+constexpr int kMaxSm = 1024;
+constexpr int kMapsPerSm = 8;
+struct alignas(128) TensorMapSlot { uint8_t bytes[128]; };
+
+// Warp-collective: slot <- param map with its row dimension (dim 2) replaced.
+__device__ __forceinline__ const CUtensorMap *patch_rows(const CUtensorMap &param_map, TensorMapSlot *slot,
+                                                         uint32_t smem_desc, uint8_t *smem_desc_gen,
+                                                         uint32_t rows, int lane) {
+  reinterpret_cast<uint32_t *>(smem_desc_gen)[lane] = reinterpret_cast<const uint32_t *>(&param_map)[lane];
+  __syncwarp();
+  if (lane == 0) tensormap_replace_dim2_smem(smem_desc, rows);
+  __syncwarp();
+  tensormap_publish(slot, smem_desc);
+  tensormap_acquire(slot);
+  return reinterpret_cast<const CUtensorMap *>(slot);
+}
+
 // ------------------------------------------------------- UMMA descriptors
 
 constexpr uint32_t kFmtF16 = 0, kFmtBF16 = 1;
