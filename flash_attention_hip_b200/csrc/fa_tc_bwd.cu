@@ -77,9 +77,9 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
-  float v;
-  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+__device__ __forceinline__ float4 ld_shared_f32x4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
   return v;
 }
 
@@ -213,7 +213,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                              c * 64, hq, qrow0 + i * kT, bcoord);
         }
         {
-          // lse2 = LSE * log2(e) (+inf past the sequence end => P = 0 there), D = rowsum(dO o O)
+          // staged NEGATED: -LSE * log2(e) (-inf past the sequence end => P = 0 there), -D = -rowsum(dO o O)
           const float *lse = a.lse + ((size_t)bidx * a.h + hq) * a.sq;
           const float *dd = a.softmax_d + ((size_t)bidx * a.h + hq) * a.sq_rounded;
           const uint32_t st = sbase + C::kStat + s * 1024;
@@ -222,8 +222,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const int r = t * 32 + lane, row = i * kT + r;
             const float l = row < sq ? lse[row] : INFINITY;
             const float dv = row < sq ? dd[row] : 0.f;
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 4 * r), "f"(l * kLog2e) : "memory");
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 512 + 4 * r), "f"(dv) : "memory");
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 4 * r), "f"(-l * kLog2e) : "memory");
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 512 + 4 * r), "f"(-dv) : "memory");
           }
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(B.q_full + 8 * s);
@@ -342,6 +342,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const int n = (warp & 3) * 32 + lane;              // key row inside the tile == TMEM lane
     const int n_abs = j * kT + n;
     const bool kv_valid = n_abs < sk;
+    const bool ragged_k = j * kT + kT > sk;            // this CTA's key tile runs past the sequence end
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const float c2 = a.scale_log2;
     uint32_t add7 = 0;
@@ -392,12 +393,19 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
       const int lim = n_abs - shift;                     // causal: visible iff q >= lim
+      const float2 c2v = make_float2(c2, c2);
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const float lse2 = ld_shared_f32(stat + 4 * c);
-        float e = exp2f(fmaf(p[c], c2, -lse2));
-        if (!kv_valid || (diag && q_base + c < lim)) e = 0.f;
-        p[c] = e;
+      for (int c = 0; c < 64; c += 4) {
+        const float4 nl = ld_shared_f32x4(stat + 4 * c);                  // -lse2 of 4 query columns
+        float2 x = __ffma2_rn(make_float2(p[c], p[c + 1]), c2v, make_float2(nl.x, nl.y));
+        float2 y = __ffma2_rn(make_float2(p[c + 2], p[c + 3]), c2v, make_float2(nl.z, nl.w));
+        p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
+        p[c + 2] = ptx::ex2(y.x); p[c + 3] = ptx::ex2(y.y);
+      }
+      if (diag || ragged_k) {                            // CTA/warp-uniform: only diagonal and last key tiles
+#pragma unroll
+        for (int c = 0; c < 64; ++c)
+          if (!kv_valid || (diag && q_base + c < lim)) p[c] = 0.f;
       }
       {
         uint32_t pk[32];
@@ -427,16 +435,21 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           ptx::tmem_ld_x32(tDP + lane_sel + w * 64 + half * 32, dp);
           ptx::tmem_wait_ld();
 #pragma unroll
-          for (int c = 0; c < 32; c += 2) {
+          for (int c = 0; c < 32; c += 4) {
             const int cq = half * 32 + c;
-            float g0 = __uint_as_float(dp[c]), g1 = __uint_as_float(dp[c + 1]);
+            float2 g01 = ptx::u2f2(dp[c], dp[c + 1]), g23 = ptx::u2f2(dp[c + 2], dp[c + 3]);
             if constexpr (kDropout) {
               const uint32_t kb = cq < 32 ? keep_lo >> cq : keep_hi >> (cq - 32);
-              g0 = (kb & 1u) ? g0 * a.rp_dropout : 0.f;
-              g1 = (kb & 2u) ? g1 * a.rp_dropout : 0.f;
+              g01.x = (kb & 1u) ? g01.x * a.rp_dropout : 0.f;
+              g01.y = (kb & 2u) ? g01.y * a.rp_dropout : 0.f;
+              g23.x = (kb & 4u) ? g23.x * a.rp_dropout : 0.f;
+              g23.y = (kb & 8u) ? g23.y * a.rp_dropout : 0.f;
             }
-            const float d0 = ld_shared_f32(stat + 512 + 4 * cq), d1 = ld_shared_f32(stat + 512 + 4 * cq + 4);
-            ds[cq / 2] = pack2(p[cq] * (g0 - d0), p[cq + 1] * (g1 - d1), kBF16);
+            const float4 nd = ld_shared_f32x4(stat + 512 + 4 * cq);        // -D of 4 query columns
+            const float2 e01 = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(g01, make_float2(nd.x, nd.y)));
+            const float2 e23 = __fmul2_rn(make_float2(p[cq + 2], p[cq + 3]), __fadd2_rn(g23, make_float2(nd.z, nd.w)));
+            ds[cq / 2] = pack2(e01.x, e01.y, kBF16);
+            ds[cq / 2 + 1] = pack2(e23.x, e23.y, kBF16);
           }
         }
       }

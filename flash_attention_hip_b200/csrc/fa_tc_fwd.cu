@@ -325,22 +325,22 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         for (int c = 0; c < 128; ++c)
           if (col0 + c > lim) s[c] = 0xff800000u;  // -inf
       }
-      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      float mx0 = m_run, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < 128; c += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(s[c]));
-        mx1 = fmaxf(mx1, __uint_as_float(s[c + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(s[c + 2]));
-        mx3 = fmaxf(mx3, __uint_as_float(s[c + 3]));
+      for (int c = 0; c < 128; c += 8) {
+        mx0 = ptx::max3(mx0, __uint_as_float(s[c]), __uint_as_float(s[c + 1]));
+        mx1 = ptx::max3(mx1, __uint_as_float(s[c + 2]), __uint_as_float(s[c + 3]));
+        mx2 = ptx::max3(mx2, __uint_as_float(s[c + 4]), __uint_as_float(s[c + 5]));
+        mx3 = ptx::max3(mx3, __uint_as_float(s[c + 6]), __uint_as_float(s[c + 7]));
       }
-      const float m_new = fmaxf(fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)), m_run);
+      const float m_new = fmaxf(ptx::max3(mx0, mx1, mx2), mx3);
       if (j == 0) {
         m_run = m_new;
       } else {
         // lazy rescale: only when some row of this warp grew by more than 2^kRescaleThreshold
         const bool grow = (m_new - m_run) * c2 > kRescaleThreshold || (m_run == -INFINITY && m_new > m_run);
         if (__any_sync(0xffffffffu, grow)) {
-          const float alpha = m_new == -INFINITY ? 1.f : exp2f((m_run - m_new) * c2);
+          const float alpha = m_new == -INFINITY ? 1.f : ptx::ex2((m_run - m_new) * c2);
           l_run *= alpha;
           m_run = m_new;
           ptx::mbar_wait(B.pv_done + 8 * t, (j - 1) & 1);   // O_t holds tiles 0..j-1
@@ -359,18 +359,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       const float m_use = m_run == -INFINITY ? 0.f : m_run;
       const float neg_mc = -m_use * c2;
-      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+      const float2 c2v = make_float2(c2, c2), nmv = make_float2(neg_mc, neg_mc);
+      float2 l01 = make_float2(0.f, 0.f), l23 = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 128; c += 4) {
-        const float p0 = exp2f(fmaf(__uint_as_float(s[c]), c2, neg_mc));
-        const float p1 = exp2f(fmaf(__uint_as_float(s[c + 1]), c2, neg_mc));
-        const float p2 = exp2f(fmaf(__uint_as_float(s[c + 2]), c2, neg_mc));
-        const float p3 = exp2f(fmaf(__uint_as_float(s[c + 3]), c2, neg_mc));
-        l0 += p0; l1 += p1; l2 += p2; l3 += p3;
-        s[c / 2] = pack_pair(p0, p1, kBF16);       // pairs land below the read cursor: c/2 < c
-        s[c / 2 + 1] = pack_pair(p2, p3, kBF16);
+        float2 a = __ffma2_rn(ptx::u2f2(s[c], s[c + 1]), c2v, nmv);
+        float2 b = __ffma2_rn(ptx::u2f2(s[c + 2], s[c + 3]), c2v, nmv);
+        a.x = ptx::ex2(a.x); a.y = ptx::ex2(a.y);
+        b.x = ptx::ex2(b.x); b.y = ptx::ex2(b.y);
+        l01 = __fadd2_rn(l01, a);
+        l23 = __fadd2_rn(l23, b);
+        s[c / 2] = pack_pair(a.x, a.y, kBF16);       // pairs land below the read cursor: c/2 < c
+        s[c / 2 + 1] = pack_pair(b.x, b.y, kBF16);
       }
-      l_run += (l0 + l1) + (l2 + l3);
+      l_run += (l01.x + l01.y) + (l23.x + l23.y);
       if constexpr (kDropout) {
         // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
 #pragma unroll

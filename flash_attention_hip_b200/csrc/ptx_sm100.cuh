@@ -214,6 +214,25 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
 }
 
 
+
+// ------------------------------------------------------------ fast math
+// MUFU.EX2 without the denormal-range fix-up code exp2f() carries (3 extra
+// instructions per call); inputs here are <= ~8, tiny results flush to zero.
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// 3-input max (FMNMX3, sm_100+).
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ float2 u2f2(uint32_t lo, uint32_t hi) {
+  return make_float2(__uint_as_float(lo), __uint_as_float(hi));
+}
+
 // ---------------------------------------------- device-side tensor-map patching
 // Packed (varlen) inputs: the host cannot know a sequence's last row (cu_seqlens
 // lives on the device), so each CTA bounds its own copy of the tensor map:
