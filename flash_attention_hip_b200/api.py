@@ -14,7 +14,9 @@ from typing import Optional, Tuple
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libflash_attn.so")
+# FA_B200_TRACE=1 selects the developer build with in-kernel event timelines (build.py --trace)
+LIB_PATH = os.path.join(_HERE, "lib", "libflash_attn_trace.so" if os.environ.get("FA_B200_TRACE") == "1"
+                        else "libflash_attn.so")
 
 PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = 0, 1, 2
 

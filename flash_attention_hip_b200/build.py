@@ -38,16 +38,18 @@ def _headers_digest() -> str:
     return h.hexdigest()
 
 
-def _compile_one(src: str, digest: str, force: bool, verbose: bool) -> str:
-    obj = os.path.join(OBJDIR, os.path.basename(src)[:-3] + ".o")
+def _compile_one(src: str, digest: str, force: bool, verbose: bool, extra=(), objdir=None) -> str:
+    objdir = objdir or OBJDIR
+    digest = digest + " ".join(extra)
+    obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
     stamp = obj + ".stamp"
     with open(src, "rb") as fh:
         key = hashlib.sha1(fh.read() + digest.encode()).hexdigest()
     if not force and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == key:
         return obj
-    cmd = [NVCC] + ARCH + FLAGS + ["-c", src, "-o", obj]
+    cmd = [NVCC] + ARCH + FLAGS + list(extra) + ["-c", src, "-o", obj]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    log = os.path.join(OBJDIR, os.path.basename(src)[:-3] + ".log")
+    log = os.path.join(objdir, os.path.basename(src)[:-3] + ".log")
     with open(log, "w") as fh:
         fh.write(r.stdout)
     if r.returncode != 0:
@@ -59,22 +61,26 @@ def _compile_one(src: str, digest: str, force: bool, verbose: bool) -> str:
     return obj
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(OBJDIR, exist_ok=True)
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True builds the developer variant libflash_attn_trace.so (-DFA_TRACE, csrc/fa_trace.cuh)."""
+    objdir = OBJDIR + ("_trace" if trace else "")
+    lib = LIB.replace(".so", "_trace.so") if trace else LIB
+    extra = ("-DFA_TRACE",) if trace else ()
+    os.makedirs(objdir, exist_ok=True)
     digest = _headers_digest()
     srcs = sources()
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        objs = list(ex.map(lambda s: _compile_one(s, digest, force, verbose), srcs))
+        objs = list(ex.map(lambda s: _compile_one(s, digest, force, verbose, extra, objdir), srcs))
     newest = max(os.path.getmtime(o) for o in objs)
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest:
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-cudart", "static", "-ccbin", "/usr/bin/g++",
+    if force or not os.path.exists(lib) or os.path.getmtime(lib) < newest:
+        cmd = [NVCC] + ARCH + ["-shared", "-o", lib] + objs + ["-cudart", "static", "-ccbin", "/usr/bin/g++",
                                                       "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map")]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout[-4000:]}")
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv)
+    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, trace="--trace" in sys.argv)
     print(path)

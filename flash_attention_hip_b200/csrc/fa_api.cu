@@ -276,6 +276,9 @@ const char *flash_attn_error(void) { return g_error.c_str(); }
 void flash_attn_b200_set_path(int path) { g_path_request = path; }
 int flash_attn_b200_last_path(void) { return g_last_path; }
 int flash_attn_b200_last_launch_count(void) { return g_last_launches; }
+int flash_attn_b200_trace_read(int kernel, int role, unsigned long long *dst, int max_events) {
+  return kernel == 0 ? fa::trace_read_fwd(dst, role, max_events) : fa::trace_read_bwd(dst, role, max_events);
+}
 const char *flash_attn_b200_version(void) { return "flash_attn_b200 0.1 (sm_100a)"; }
 
 }  // extern "C"

@@ -94,4 +94,8 @@ const char *launch_tc_fwd(const Params &p, cudaStream_t stream);
 bool tc_bwd_supported(const Params &p);
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream);
 
+// Event timelines of a -DFA_TRACE build (0 events otherwise); see fa_trace.cuh.
+int trace_read_bwd(unsigned long long *dst, int role, int max_events);
+int trace_read_fwd(unsigned long long *dst, int role, int max_events);
+
 }  // namespace fa

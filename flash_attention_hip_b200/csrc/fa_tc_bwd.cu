@@ -23,6 +23,7 @@
 #include "fa_common.cuh"
 #include "ptx_sm100.cuh"
 #include "tma_host.cuh"
+#include "fa_trace.cuh"
 
 namespace fa {
 
@@ -119,6 +120,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
               const BwdArgs a) {
   using C = Cfg<D>;
+  // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
+  // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
+  constexpr bool kEarlyDrain = !kDropout;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t sbase = ptx::smem_u32(smem_raw);
   if (sbase & 1023u) __trap();   // the swizzled tiles need a 1024-byte aligned base
@@ -178,6 +182,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 384;
 
+#ifdef FA_TRACE
+  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0;
+#endif
   if (warp >= 8 && warp < 12) {
     // =========================== producer warpgroup ======================================
     ptx::setmaxnreg_dec<32>();
@@ -243,89 +250,117 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       constexpr uint32_t id_mn_mn = ptx::make_idesc(fmt, ptx::kMajorMN, ptx::kMajorMN, kT, D); // (5)
       constexpr uint64_t hi_k = ptx::make_smem_desc_hi(16, 1024);
       constexpr uint64_t hi_mn = ptx::make_smem_desc_hi(C::kSub, 1024);
-      // D(tmem) = A(K-major smem) * B(K-major smem), contraction over d
-      auto gemm_kk = [&](uint32_t d_tmem, uint32_t a_smem, uint32_t b_smem) {
+      // D(tmem) = A(K-major smem) * B(K-major smem), contraction over d; a_off/b_off: bytes from sbase
+      auto gemm_kk = [&](uint32_t d_tmem, uint32_t a16, uint32_t a_off, uint32_t b16, uint32_t b_off) {
 #pragma unroll
         for (int ks = 0; ks < D / 16; ++ks) {
           const uint32_t off = (ks / 4) * C::kSub + (ks % 4) * 32;
-          ptx::mma_ss(d_tmem, ptx::smem_desc(hi_k, a_smem + off), ptx::smem_desc(hi_k, b_smem + off), id_kk, ks > 0);
+          ptx::mma_ss(d_tmem, ptx::smem_desc_at(hi_k, a16, a_off + off), ptx::smem_desc_at(hi_k, b16, b_off + off),
+                      id_kk, ks > 0);
         }
       };
+      FA_TRACE_DECL(tr, 0, tr_cta);
       ptx::mbar_wait(B.kv_full, 0);
       ptx::tc_fence_after();
       if (n_it > 0) {
         ptx::mbar_wait(B.q_full, 0);
         ptx::tc_fence_after();
-        gemm_kk(tS, sbase + C::kK, sbase + C::kQ);                       // (1) S^T(0)
+        gemm_kk(tS, sbase >> 4, C::kK, sbase >> 4, C::kQ);                         // (1) S^T(0)
         ptx::mma_commit(B.s_full);
       }
       for (int it = 0; it < n_it; ++it) {
         const int s = it & 1;
-        const uint32_t qa = sbase + C::kQ + s * C::kTile;
+        // descriptors are rebuilt from this laundered base every iteration (see smem_desc_at)
+        const uint32_t b16 = ptx::opaque(sbase >> 4);
+        const uint32_t q16 = b16 + s * (C::kTile >> 4), qn16 = b16 + (s ^ 1) * (C::kTile >> 4);
+        FA_TRACE_EV(tr, 1);
         ptx::mbar_wait(B.do_full, it & 1);
+        FA_TRACE_EV(tr, 2);
         if (it > 0) ptx::mbar_wait(B.dq_drained, (it - 1) & 1);           // dP^T shares TMEM with dQ
         ptx::tc_fence_after();
-        gemm_kk(tDP, sbase + C::kV, sbase + C::kDO);                      // (2) dP^T(it)
+        FA_TRACE_EV(tr, 3);
+        gemm_kk(tDP, b16, C::kV, b16, C::kDO);                               // (2) dP^T(it)
         ptx::mma_commit(B.dp_full);
         ptx::mbar_wait(B.p_ready, it & 1);
         ptx::tc_fence_after();
+        FA_TRACE_EV(tr, 4);
 #pragma unroll
         for (int ks = 0; ks < kT / 16; ++ks)                               // (3) dV += P^T dO
           ptx::mma_ts(tDV, tS + (ks / 4) * 64 + (ks % 4) * 8,
-                      ptx::smem_desc(hi_mn, sbase + C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
+                      ptx::smem_desc_at(hi_mn, b16, C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
         ptx::mma_commit(B.do_empty);
         if (it + 1 < n_it) {
           ptx::mbar_wait(B.q_full + 8 * (s ^ 1), ((it + 1) >> 1) & 1);
           ptx::tc_fence_after();
-          gemm_kk(tS, sbase + C::kK, sbase + C::kQ + (s ^ 1) * C::kTile);  // (1) S^T(it+1)
+          gemm_kk(tS, b16, C::kK, qn16, C::kQ);                          // (1) S^T(it+1)
           ptx::mma_commit(B.s_full);
         }
+        FA_TRACE_EV(tr, 5);
         ptx::mbar_wait(B.ds_ready, it & 1);
         ptx::tc_fence_after();
+        FA_TRACE_EV(tr, 6);
 #pragma unroll
         for (int ks = 0; ks < kT / 16; ++ks) {                             // (4) dK += dS^T Q
           const uint32_t aoff = (ks / 4) * C::kSub + (ks % 4) * 32;
-          ptx::mma_ss(tDK, ptx::smem_desc(hi_k, sbase + C::kDS + aoff), ptx::smem_desc(hi_mn, qa + ks * 2048),
+          ptx::mma_ss(tDK, ptx::smem_desc_at(hi_k, b16, C::kDS + aoff), ptx::smem_desc_at(hi_mn, q16, C::kQ + ks * 2048),
                       id_k_mn, it > 0 || ks > 0);
         }
         ptx::mma_commit(B.q_empty + 8 * s);
 #pragma unroll
         for (int ks = 0; ks < kT / 16; ++ks)                               // (5) dQ = dS K
-          ptx::mma_ss(tDP, ptx::smem_desc(hi_mn, sbase + C::kDS + ks * 2048),
-                      ptx::smem_desc(hi_mn, sbase + C::kK + ks * 2048), id_mn_mn, ks > 0);
+          ptx::mma_ss(tDP, ptx::smem_desc_at(hi_mn, b16, C::kDS + ks * 2048),
+                      ptx::smem_desc_at(hi_mn, b16, C::kK + ks * 2048), id_mn_mn, ks > 0);
         ptx::mma_commit(B.dq_full);
       }
       ptx::mma_commit(B.acc_done);
     }
   } else if (warp >= kDrainWarp0) {
     // =========================== dQ drain warpgroup ======================================
-    ptx::setmaxnreg_dec<80>();
+    // register split (16 warps x 128 = 2048 per lane): without dropout the drain warps hold a whole
+    // dQ tile (208), with dropout the compute warps need the room for the keep-bit exchange
+    if constexpr (!kEarlyDrain) ptx::setmaxnreg_dec<80>();
+    else ptx::setmaxnreg_inc<D == 128 ? 208 : 128>();
     const int dw = warp - kDrainWarp0;                 // == warp % 4: TMEM lane quadrant
     const int r = dw * 32 + lane;                      // query row inside the tile == TMEM lane
     const uint32_t lane_sel = (uint32_t)(dw * 32) << 16;
     const bool leader = (warp == kDrainWarp0 && lane == 0);
     uint32_t cc = 0;                                   // running 16 KB block counter (staging ring of 2)
+    FA_TRACE_DECL(trd, 1, tr_cta && leader);
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = i_min + it % n_i;
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
       float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * (D / 32)) * 4096;
+      FA_TRACE_EV(trd, 20);
       ptx::mbar_wait(B.dq_full, it & 1);
       ptx::tc_fence_after();
+      FA_TRACE_EV(trd, 21);
+      // kEarlyDrain: the whole dQ tile -> registers first, so dP^T(it+1) may reuse the TMEM columns at once
+      uint32_t v[kEarlyDrain ? D / 32 : 1][32];
+      if constexpr (kEarlyDrain) {
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) ptx::tmem_ld_x32(tDP + lane_sel + c * 32, v[c]);
+        ptx::tmem_wait_ld();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(B.dq_drained);
+      }
+      FA_TRACE_EV(trd, 22);
 #pragma unroll
       for (int c = 0; c < D / 32; ++c, ++cc) {
-        uint32_t v[32];
-        ptx::tmem_ld_x32(tDP + lane_sel + c * 32, v);
-        ptx::tmem_wait_ld();
-        if (c == D / 32 - 1) {                         // TMEM tile fully read: dP^T(it+1) may overwrite it
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(B.dq_drained);
+        uint32_t(&vc)[32] = v[kEarlyDrain ? c : 0];
+        if constexpr (!kEarlyDrain) {
+          ptx::tmem_ld_x32(tDP + lane_sel + c * 32, vc);
+          ptx::tmem_wait_ld();
+          if (c == D / 32 - 1) {                       // TMEM tile fully read: dP^T(it+1) may overwrite it
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(B.dq_drained);
+          }
         }
         const uint32_t buf = sbase + C::kDQ + (cc & 1) * 16384;
         if (leader && cc >= 2) ptx::tma_store_wait_read<1>();   // the block that used `buf` has been read
         ptx::named_bar_sync(1, 128);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          st_shared_v4(buf + r * 128 + ((k ^ (r & 7)) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+          st_shared_v4(buf + r * 128 + ((k ^ (r & 7)) << 4), vc[4 * k], vc[4 * k + 1], vc[4 * k + 2], vc[4 * k + 3]);
         ptx::fence_proxy_async_smem();
         ptx::named_bar_sync(1, 128);
         if (leader) {
@@ -337,7 +372,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (leader) ptx::tma_store_wait<0>();
   } else {
     // =========================== compute warps ============================================
-    ptx::setmaxnreg_inc<200>();
+    if constexpr (!kEarlyDrain) ptx::setmaxnreg_inc<200>();
+    else ptx::setmaxnreg_inc<D == 128 ? 136 : 176>();
     const int w = warp >> 2;                           // which 64 query columns
     const int n = (warp & 3) * 32 + lane;              // key row inside the tile == TMEM lane
     const int n_abs = j * kT + n;
@@ -352,9 +388,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       t_msb = a.drop_threshold >= 128u;
     }
 
+    FA_TRACE_DECL(trc, 2 + w, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = i_min + it % n_i;
       const int s = it & 1;
+      FA_TRACE_EV(trc, 10);
       const uint32_t stat = sbase + C::kStat + s * 1024 + w * 256;   // lse2 / D of my 64 query columns
       const int q_base = i * kT + w * 64;
 
@@ -381,8 +419,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
 
       ptx::mbar_wait(B.q_full + 8 * s, (it >> 1) & 1);   // LSE / D staged
+      FA_TRACE_EV(trc, 11);
       ptx::mbar_wait(B.s_full, it & 1);
       ptx::tc_fence_after();
+      FA_TRACE_EV(trc, 12);
       float p[64];
       {
         uint32_t(&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&p[0]);
@@ -424,9 +464,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(B.p_ready);
+      FA_TRACE_EV(trc, 13);
 
       ptx::mbar_wait(B.dp_full, it & 1);
       ptx::tc_fence_after();
+      FA_TRACE_EV(trc, 14);
       uint32_t ds[32];
       {
         uint32_t dp[32];
@@ -453,7 +495,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           }
         }
       }
+      FA_TRACE_EV(trc, 15);
       if (it > 0) ptx::mbar_wait(B.dq_full, (it - 1) & 1);   // GEMMs (4),(5) of it-1 have read dS^T
+      FA_TRACE_EV(trc, 16);
       {
         const uint32_t rowp = sbase + C::kDS + w * C::kSub + n * 128;
 #pragma unroll
@@ -463,6 +507,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(B.ds_ready);
+      FA_TRACE_EV(trc, 17);
     }
 
     // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
@@ -592,6 +637,15 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
 }
 
 }  // namespace
+
+int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
+#ifdef FA_TRACE
+  return trace::read_events(dst, role, max_events);
+#else
+  (void)dst; (void)role; (void)max_events;
+  return 0;
+#endif
+}
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d != 64 && p.d != 128) return false;

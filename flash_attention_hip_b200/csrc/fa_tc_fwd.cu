@@ -23,6 +23,7 @@
 #include "fa_common.cuh"
 #include "ptx_sm100.cuh"
 #include "tma_host.cuh"
+#include "fa_trace.cuh"
 
 namespace fa {
 
@@ -180,6 +181,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+#ifdef FA_TRACE
+  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0;
+#endif
 
   if (warp >= 8) {
     // ======================= producer warpgroup ================================
@@ -242,6 +246,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           ptx::mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kPOff + ks * 8,
                       ptx::smem_desc(hi_mn, va + ks * 2048), idesc_pv, acc || ks > 0);
       };
+      FA_TRACE_DECL(tr, 0, tr_cta);
+      FA_TRACE_EV(tr, 1);
       ptx::mbar_wait(B.q_full, 0);
       ptx::tc_fence_after();
       if (nmax > 0) {
@@ -254,10 +260,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       for (int j = 0; j < nmax; ++j) {
         const int s = j % C::kStages, sn = (j + 1) % C::kStages;
         const uint32_t ph = (j / C::kStages) & 1, phn = ((j + 1) / C::kStages) & 1;
+        FA_TRACE_EV(tr, 2);
         ptx::mbar_wait(B.v_full + 8 * s, ph);
+        FA_TRACE_EV(tr, 3);
         if (j < ntile[0]) {
           ptx::mbar_wait(B.p_full, j & 1);
           ptx::tc_fence_after();
+          FA_TRACE_EV(tr, 4);
           pv(0, s, j > 0);
           ptx::mma_commit(B.pv_done);
         }
@@ -265,10 +274,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           ptx::mbar_wait(B.k_full + 8 * sn, phn);
           ptx::tc_fence_after();
         }
+        FA_TRACE_EV(tr, 5);
         if (j + 1 < ntile[0]) { qk(0, sn); ptx::mma_commit(B.s_full); }
+        FA_TRACE_EV(tr, 6);
         if (j < ntile[1]) {
           ptx::mbar_wait(B.p_full + 8, j & 1);
           ptx::tc_fence_after();
+          FA_TRACE_EV(tr, 7);
           pv(1, s, j > 0);
           ptx::mma_commit(B.pv_done + 8);
         }
@@ -301,9 +313,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     }
 
     float m_run = -INFINITY, l_run = 0.f;
+    FA_TRACE_DECL(trs, 1 + t, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int j = 0; j < n_t; ++j) {
+      FA_TRACE_EV(trs, 10);
       ptx::mbar_wait(B.s_full + 8 * t, j & 1);
       ptx::tc_fence_after();
+      FA_TRACE_EV(trs, 11);
       uint32_t s[128];
       {
         uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
@@ -316,6 +331,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_ld_x32(tS + 96, s3);
         ptx::tmem_wait_ld();
       }
+      FA_TRACE_EV(trs, 12);
       const int col0 = j * kTileN;
       // masking is needed only on the diagonal and on the ragged last tile (warp-uniform test)
       const bool need_mask = (col0 + kTileN > sk) || (a.causal && col0 + kTileN - 1 > tile_row0 + shift);
@@ -357,6 +373,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           ptx::tmem_wait_st();
         }
       }
+      FA_TRACE_EV(trs, 13);
       const float m_use = m_run == -INFINITY ? 0.f : m_run;
       const float neg_mc = -m_use * c2;
       const float2 c2v = make_float2(c2, c2), nmv = make_float2(neg_mc, neg_mc);
@@ -373,6 +390,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         s[c / 2 + 1] = pack_pair(b.x, b.y, kBF16);
       }
       l_run += (l01.x + l01.y) + (l23.x + l23.y);
+      FA_TRACE_EV(trs, 14);
       if constexpr (kDropout) {
         // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
 #pragma unroll
@@ -397,6 +415,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(B.p_full + 8 * t);
+      FA_TRACE_EV(trs, 15);
     }
 
     // ---- epilogue: O_t / l -> global, LSE ------------------------------------------
@@ -447,6 +466,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------
+
+int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
+#ifdef FA_TRACE
+  return trace::read_events(dst, role, max_events);
+#else
+  (void)dst; (void)role; (void)max_events;
+  return 0;
+#endif
+}
 
 bool tc_fwd_supported(const Params &p) {
   if (p.d != 64 && p.d != 128) return false;

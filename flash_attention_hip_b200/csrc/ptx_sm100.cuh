@@ -312,5 +312,18 @@ __device__ __forceinline__ uint64_t smem_desc(uint64_t hi, uint32_t smem_addr) {
   return hi | uint64_t((smem_addr >> 4) & 0x3fff);
 }
 
+// Descriptor from a laundered base: `base16` = (CTA smem base >> 4) passed through opaque() once per
+// loop iteration, `off` a compile-time byte offset.  One IADD per descriptor instead of a hoisted
+// (and, in a 32-register MMA warp, spilled) table of 64-bit constants.
+__device__ __forceinline__ uint64_t smem_desc_at(uint64_t hi, uint32_t base16, uint32_t off) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(base16 + (off >> 4) + (uint32_t)hi), "r"((uint32_t)(hi >> 32)));
+  return d;
+}
+__device__ __forceinline__ uint32_t opaque(uint32_t x) {
+  asm volatile("" : "+r"(x));
+  return x;
+}
+
 }  // namespace ptx
 }  // namespace fa

@@ -34,6 +34,11 @@ int flash_attn_b200_last_path(void);
 /* Number of kernel launches the last successful call on this thread enqueued. */
 int flash_attn_b200_last_launch_count(void);
 
+/* Developer builds only (-DFA_TRACE): copies the in-kernel event timeline of warp role `role`
+ * of the forward (kernel 0) or backward (kernel 1) tcgen05 kernel's traced CTA into dst as
+ * (clock64 << 8 | event id) words; synchronises the device.  Product builds return 0. */
+int flash_attn_b200_trace_read(int kernel, int role, unsigned long long *dst, int max_events);
+
 /* Library version string, e.g. "flash_attn_b200 0.1 (sm_100a)". */
 const char *flash_attn_b200_version(void);
 
