@@ -14,9 +14,10 @@ from typing import Optional, Tuple
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# FA_B200_TRACE=1 selects the developer build with in-kernel event timelines (build.py --trace)
-LIB_PATH = os.path.join(_HERE, "lib", "libflash_attn_trace.so" if os.environ.get("FA_B200_TRACE") == "1"
-                        else "libflash_attn.so")
+# developer builds: FA_B200_TRACE=1 -> in-kernel event timelines (build.py --trace);
+# FA_B200_VARIANT=x -> a tuning variant (build.py --variant=x -D...)
+_VARIANT = "trace" if os.environ.get("FA_B200_TRACE") == "1" else os.environ.get("FA_B200_VARIANT", "")
+LIB_PATH = os.path.join(_HERE, "lib", "libflash_attn" + ("_" + _VARIANT if _VARIANT else "") + ".so")
 
 PATH_AUTO, PATH_GENERIC, PATH_TCGEN05 = 0, 1, 2
 

@@ -61,11 +61,14 @@ def _compile_one(src: str, digest: str, force: bool, verbose: bool, extra=(), ob
     return obj
 
 
-def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
-    """trace=True builds the developer variant libflash_attn_trace.so (-DFA_TRACE, csrc/fa_trace.cuh)."""
-    objdir = OBJDIR + ("_trace" if trace else "")
-    lib = LIB.replace(".so", "_trace.so") if trace else LIB
-    extra = ("-DFA_TRACE",) if trace else ()
+def build(force: bool = False, verbose: bool = False, trace: bool = False, variant: str = "", defs=()) -> str:
+    """trace=True builds the developer variant libflash_attn_trace.so (-DFA_TRACE, csrc/fa_trace.cuh).
+    variant="x", defs=("-DFOO=1",) builds a tuning variant libflash_attn_x.so (api.py: FA_B200_VARIANT=x)."""
+    if trace:
+        variant, defs = variant or "trace", tuple(defs) + ("-DFA_TRACE",)
+    objdir = OBJDIR + ("_" + variant if variant else "")
+    lib = LIB.replace(".so", "_" + variant + ".so") if variant else LIB
+    extra = tuple(defs)
     os.makedirs(objdir, exist_ok=True)
     digest = _headers_digest()
     srcs = sources()
@@ -82,5 +85,7 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> st
 
 
 if __name__ == "__main__":
-    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, trace="--trace" in sys.argv)
+    var = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--variant=")]
+    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, trace="--trace" in sys.argv,
+                 variant=var[0] if var else "", defs=[a for a in sys.argv if a.startswith("-D")])
     print(path)

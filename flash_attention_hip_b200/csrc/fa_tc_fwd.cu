@@ -20,6 +20,7 @@
 // The running max is updated lazily: O_t is rescaled (by the softmax warps
 // themselves) only when the max grew by more than 2^8, which keeps P <= 256 in
 // bf16 and takes the rescale off the steady-state critical path.
+#include <type_traits>
 #include "fa_common.cuh"
 #include "ptx_sm100.cuh"
 #include "tma_host.cuh"
@@ -35,6 +36,13 @@ constexpr int kThreads = 384;
 constexpr int kMmaWarp = 8, kLoadWarp = 9;
 constexpr uint32_t kPOff = 32;     // P's first column inside its S tile
 constexpr float kRescaleThreshold = 8.0f;  // in log2 units
+#ifndef FA_EMU_PER8
+#define FA_EMU_PER8 0
+#endif
+// Exponentials per 8 computed on the FMA pipe (ptx::ex2_poly2) instead of MUFU.  Measured on B200
+// (S4096 D128, build.py --variant): 0 -> 1075, 2 -> 1057, 4 -> 1018, 6 -> 981 TFLOP/s causal: the
+// softmax is bound by the S -> P -> PV -> QK dependency chain and by issue slots, not by MUFU.
+constexpr int kEmuPer8 = FA_EMU_PER8;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -47,7 +55,7 @@ struct Cfg {
   static constexpr uint32_t kSmemK = 2 * kTileBytes;
   static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
   static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
-  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 6;
+  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8;
   static constexpr uint32_t kSmemDesc = kSmemBar + 256;       // 3 x 128 B tensor-map staging (packed inputs)
   static constexpr uint32_t kSmemBytes = kSmemDesc + 3 * 128 + 1024;  // + alignment slack
   static_assert(kNumBars * 8 + 16 <= 256, "barrier block overflows");
@@ -58,7 +66,7 @@ struct Cfg {
 __device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][3];
 
 struct Bars {
-  uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_full, pv_done;  // first of each group
+  uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_lo, p_hi, pv_done;  // first of each group
 };
 
 __device__ __forceinline__ uint32_t pack_pair(float lo, float hi, bool bf16) {
@@ -149,8 +157,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   B.v_full = B.k_empty + 8 * C::kStages;
   B.v_empty = B.v_full + 8 * C::kStages;
   B.s_full = B.v_empty + 8 * C::kStages;
-  B.p_full = B.s_full + 16;
-  B.pv_done = B.p_full + 16;
+  B.p_lo = B.s_full + 16;
+  B.p_hi = B.p_lo + 16;
+  B.pv_done = B.p_hi + 16;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + C::kSmemBar + C::kNumBars * 8);
 
   if (threadIdx.x == 0) {
@@ -163,7 +172,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     }
     for (int t = 0; t < 2; ++t) {
       ptx::mbar_init(B.s_full + 8 * t, 1);
-      ptx::mbar_init(B.p_full + 8 * t, kTileM);
+      ptx::mbar_init(B.p_lo + 8 * t, kTileM);
+      ptx::mbar_init(B.p_hi + 8 * t, kTileM);
       ptx::mbar_init(B.pv_done + 8 * t, 1);
     }
     ptx::fence_mbar_init();
@@ -229,22 +239,30 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       constexpr uint32_t idesc_pv = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorMN, kTileM, D);
       constexpr uint64_t hi_k = ptx::make_smem_desc_hi(16, 1024);             // K-major operands
       constexpr uint64_t hi_mn = ptx::make_smem_desc_hi(C::kSubBytes, 1024);  // V: MN-major
+      // descriptors are rebuilt each iteration from a laundered base (ptx::smem_desc_at): a hoisted
+      // table of 64-bit descriptors does not fit this warp's 40 registers
+      uint32_t b16 = sbase >> 4;
       auto qk = [&](int t, int stage) {
-        const uint32_t qa = sbase + C::kSmemQ + t * C::kTileBytes;
-        const uint32_t ka = sbase + C::kSmemK + stage * C::kTileBytes;
+        const uint32_t ka16 = b16 + stage * (C::kTileBytes >> 4);
 #pragma unroll
         for (int ks = 0; ks < D / 16; ++ks) {
           const uint32_t off = (ks / 4) * C::kSubBytes + (ks % 4) * 32;
-          ptx::mma_ss(tmem + t * 128, ptx::smem_desc(hi_k, qa + off), ptx::smem_desc(hi_k, ka + off),
-                      idesc_qk, ks > 0);
+          ptx::mma_ss(tmem + t * 128, ptx::smem_desc_at(hi_k, b16 + t * (C::kTileBytes >> 4), C::kSmemQ + off),
+                      ptx::smem_desc_at(hi_k, ka16, C::kSmemK + off), idesc_qk, ks > 0);
         }
       };
-      auto pv = [&](int t, int stage, bool acc) {
-        const uint32_t va = sbase + C::kSmemV + stage * C::kTileBytes;
+      // O_t (+)= P_t V: the two 64-key halves of P arrive separately (p_lo, p_hi)
+      auto pv = [&](int t, int stage, bool acc, uint32_t parity) {
+        const uint32_t va16 = b16 + stage * (C::kTileBytes >> 4);
 #pragma unroll
-        for (int ks = 0; ks < kTileN / 16; ++ks)
+        for (int ks = 0; ks < kTileN / 16; ++ks) {
+          if (ks == 0 || ks == kTileN / 32) {
+            ptx::mbar_wait((ks ? B.p_hi : B.p_lo) + 8 * t, parity);
+            ptx::tc_fence_after();
+          }
           ptx::mma_ts(tmem + 256 + t * 128, tmem + t * 128 + kPOff + ks * 8,
-                      ptx::smem_desc(hi_mn, va + ks * 2048), idesc_pv, acc || ks > 0);
+                      ptx::smem_desc_at(hi_mn, va16, C::kSmemV + ks * 2048), idesc_pv, acc || ks > 0);
+        }
       };
       FA_TRACE_DECL(tr, 0, tr_cta);
       FA_TRACE_EV(tr, 1);
@@ -253,22 +271,34 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if (nmax > 0) {
         ptx::mbar_wait(B.k_full, 0);
         ptx::tc_fence_after();
+        FA_TRACE_EV(tr, 20);
         if (ntile[0] > 0) { qk(0, 0); ptx::mma_commit(B.s_full); }
         if (ntile[1] > 0) { qk(1, 0); ptx::mma_commit(B.s_full + 8); }
         ptx::mma_commit(B.k_empty);
+#ifdef FA_TRACE
+        FA_TRACE_EV(tr, 21);                 // 20->21: issue of 16 SS MMAs on an idle pipe
+        ptx::mbar_wait(B.s_full + 8, 0);
+        FA_TRACE_EV(tr, 22);                 // 20->22: their execution
+#endif
       }
       for (int j = 0; j < nmax; ++j) {
         const int s = j % C::kStages, sn = (j + 1) % C::kStages;
         const uint32_t ph = (j / C::kStages) & 1, phn = ((j + 1) / C::kStages) & 1;
+        b16 = ptx::opaque(sbase >> 4);
         FA_TRACE_EV(tr, 2);
         ptx::mbar_wait(B.v_full + 8 * s, ph);
         FA_TRACE_EV(tr, 3);
         if (j < ntile[0]) {
-          ptx::mbar_wait(B.p_full, j & 1);
-          ptx::tc_fence_after();
           FA_TRACE_EV(tr, 4);
-          pv(0, s, j > 0);
+          pv(0, s, j > 0, j & 1);
           ptx::mma_commit(B.pv_done);
+#ifdef FA_TRACE
+          if (j == 1) {
+            FA_TRACE_EV(tr, 24);             // 4->24: wait P + issue 8 TS MMAs
+            ptx::mbar_wait(B.pv_done, 1);
+            FA_TRACE_EV(tr, 25);             // 24->25: drain
+          }
+#endif
         }
         if (j + 1 < nmax) {
           ptx::mbar_wait(B.k_full + 8 * sn, phn);
@@ -278,10 +308,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (j + 1 < ntile[0]) { qk(0, sn); ptx::mma_commit(B.s_full); }
         FA_TRACE_EV(tr, 6);
         if (j < ntile[1]) {
-          ptx::mbar_wait(B.p_full + 8, j & 1);
-          ptx::tc_fence_after();
           FA_TRACE_EV(tr, 7);
-          pv(1, s, j > 0);
+          pv(1, s, j > 0, j & 1);
           ptx::mma_commit(B.pv_done + 8);
         }
         ptx::mma_commit(B.v_empty + 8 * s);
@@ -378,43 +406,57 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       const float neg_mc = -m_use * c2;
       const float2 c2v = make_float2(c2, c2), nmv = make_float2(neg_mc, neg_mc);
       float2 l01 = make_float2(0.f, 0.f), l23 = make_float2(0.f, 0.f);
+      // P = exp2(S c2 - m c2) for 64 columns -> 32 packed words, in place (pairs land below the
+      // read cursor).  kEmu of every 8 exponentials run on the FMA pipe (ptx::ex2_poly2), the rest
+      // on MUFU; tiles with masked (-inf) entries use MUFU only so that masked P is exactly 0.
+      auto exp_half = [&](auto emu_tag, int half) {
+        constexpr int kEmu = decltype(emu_tag)::value;
 #pragma unroll
-      for (int c = 0; c < 128; c += 4) {
-        float2 a = __ffma2_rn(ptx::u2f2(s[c], s[c + 1]), c2v, nmv);
-        float2 b = __ffma2_rn(ptx::u2f2(s[c + 2], s[c + 3]), c2v, nmv);
-        a.x = ptx::ex2(a.x); a.y = ptx::ex2(a.y);
-        b.x = ptx::ex2(b.x); b.y = ptx::ex2(b.y);
-        l01 = __fadd2_rn(l01, a);
-        l23 = __fadd2_rn(l23, b);
-        s[c / 2] = pack_pair(a.x, a.y, kBF16);       // pairs land below the read cursor: c/2 < c
-        s[c / 2 + 1] = pack_pair(b.x, b.y, kBF16);
-      }
-      l_run += (l01.x + l01.y) + (l23.x + l23.y);
-      FA_TRACE_EV(trs, 14);
-      if constexpr (kDropout) {
-        // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
+        for (int c8 = 0; c8 < 64; c8 += 8) {
 #pragma unroll
-        for (int cb = 0; cb < 8; ++cb) {
-          const fa_philox4_t rnd = fa_philox4x32((uint32_t)row, (uint32_t)(col0 / 16 + cb), bh, a.ctr3,
-                                                 a.key0, a.key1);
-#pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            uint32_t m01, m23;
-            keep_masks(rnd.v[w], dc, m01, m23);
-            s[cb * 8 + w * 2] &= m01;
-            s[cb * 8 + w * 2 + 1] &= m23;
+          for (int pr = 0; pr < 4; ++pr) {
+            const int c = half * 64 + c8 + 2 * pr;
+            float2 x = __ffma2_rn(ptx::u2f2(s[c], s[c + 1]), c2v, nmv);
+            if (2 * pr < kEmu) {
+              x = ptx::ex2_poly2(x);
+            } else {
+              x.x = ptx::ex2(x.x);
+              x.y = ptx::ex2(x.y);
+            }
+            if (pr & 1) l23 = __fadd2_rn(l23, x);
+            else l01 = __fadd2_rn(l01, x);
+            s[c / 2] = pack_pair(x.x, x.y, kBF16);
           }
         }
-      }
-      {
-        uint32_t(&p0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
-        uint32_t(&p1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
-        ptx::tmem_st_x32(tP, p0);
-        ptx::tmem_st_x32(tP + 32, p1);
+      };
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        if (need_mask) exp_half(std::integral_constant<int, 0>{}, half);
+        else exp_half(std::integral_constant<int, kEmuPer8>{}, half);
+        if constexpr (kDropout) {
+          // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
+#pragma unroll
+          for (int cb = half * 4; cb < half * 4 + 4; ++cb) {
+            const fa_philox4_t rnd = fa_philox4x32((uint32_t)row, (uint32_t)(col0 / 16 + cb), bh, a.ctr3,
+                                                   a.key0, a.key1);
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+              uint32_t m01, m23;
+              keep_masks(rnd.v[w], dc, m01, m23);
+              s[cb * 8 + w * 2] &= m01;
+              s[cb * 8 + w * 2 + 1] &= m23;
+            }
+          }
+        }
+        // hand P over in halves: O += P[:, :64] V[:64] starts while the second half is exponentiated
+        uint32_t(&ph)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[half * 32]);
+        ptx::tmem_st_x32(tP + half * 32, ph);
         ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive((half ? B.p_hi : B.p_lo) + 8 * t);
+        if (half == 0) FA_TRACE_EV(trs, 14);
       }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(B.p_full + 8 * t);
+      l_run += (l01.x + l01.y) + (l23.x + l23.y);
       FA_TRACE_EV(trs, 15);
     }
 

@@ -232,6 +232,27 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
 __device__ __forceinline__ float2 u2f2(uint32_t lo, uint32_t hi) {
   return make_float2(__uint_as_float(lo), __uint_as_float(hi));
 }
+// 2^x for a pair on the FMA pipe (no MUFU: B200's 16 ex2/clk/SM is what bounds a 128x128 softmax
+// tile).  Cody-Waite: t = x + 1.5*2^23 leaves round(x) in t's low mantissa bits, xf = x - round(x)
+// in [-0.5, 0.5], degree-3 minimax polynomial (max relative error 7.5e-5, far below bf16 rounding),
+// exponent added with an integer shift-add.  x is clamped at -125, so -inf gives 2^-125, not 0:
+// callers use ex2() on tiles that hold masked entries.
+__device__ __forceinline__ float2 ex2_poly2(float2 x) {
+  const float kM = 12582912.f;
+  x.x = fmaxf(x.x, -125.f);
+  x.y = fmaxf(x.y, -125.f);
+  const float2 t = __fadd2_rn(x, make_float2(kM, kM));
+  const float2 xi = __fadd2_rn(t, make_float2(-kM, -kM));
+  const float2 xf = __ffma2_rn(xi, make_float2(-1.f, -1.f), x);
+  float2 p = __ffma2_rn(make_float2(0.055171459913253784f, 0.055171459913253784f), xf,
+                        make_float2(0.2426108568906784f, 0.2426108568906784f));
+  p = __ffma2_rn(p, xf, make_float2(0.6932609677314758f, 0.6932609677314758f));
+  p = __ffma2_rn(p, xf, make_float2(0.9999281167984009f, 0.9999281167984009f));
+  float2 r;
+  r.x = __uint_as_float(__float_as_uint(p.x) + (__float_as_uint(t.x) << 23));
+  r.y = __uint_as_float(__float_as_uint(p.y) + (__float_as_uint(t.y) << 23));
+  return r;
+}
 
 // ---------------------------------------------- device-side tensor-map patching
 // Packed (varlen) inputs: the host cannot know a sequence's last row (cu_seqlens

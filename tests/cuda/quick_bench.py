@@ -20,7 +20,9 @@ def time_fwd(b, s, h, d, causal, p=0.0, iters=20, dtype=torch.bfloat16):
     fl = 4.0 * b * h * s * s * d * (0.5 if causal else 1.0)
     print(f"fwd b{b} s{s} h{h} d{d} causal={causal} p={p} path={api.last_path()}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
 
-if __name__ == "__main__":
+WHICH = sys.argv[1] if len(sys.argv) > 1 else "all"
+
+if __name__ == "__main__" and WHICH in ("all", "fwd"):
     time_fwd(8, 2048, 16, 128, True)
     time_fwd(16, 4096, 32, 128, True)
     time_fwd(16, 4096, 32, 128, True, p=0.1)
@@ -52,7 +54,7 @@ def time_bwd(b, s, h, d, causal, p=0.0, iters=10, dtype=torch.bfloat16, hk=None)
     print(f"bwd b{b} s{s} h{h}/{hk} d{d} causal={causal} p={p} path={api.last_path()}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s", flush=True)
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and WHICH in ("all", "bwd"):
     time_bwd(8, 2048, 16, 128, True)
     time_bwd(16, 4096, 32, 128, True)
     time_bwd(16, 4096, 32, 128, True, p=0.1)

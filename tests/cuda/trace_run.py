@@ -2,7 +2,7 @@
 (cycles between consecutive events, averaged over the steady-state iterations).
   FA_B200_TRACE=1 python tests/cuda/trace_run.py [fwd|bwd] [p_dropout] [causal 0/1]"""
 import ctypes, os, sys, collections
-os.environ["FA_B200_TRACE"] = "1"
+os.environ.setdefault("FA_B200_VARIANT", "trace")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from flash_attention_hip_b200 import api
@@ -40,6 +40,9 @@ for role in range(8):
         agg[(ev[i - 1][1], ev[i][1])].append(ev[i][0] - ev[i - 1][0])
     for (a, b_), vals in sorted(agg.items()):
         print(f"   {a:3d} -> {b_:3d}: mean {sum(vals) / len(vals):8.0f}  min {min(vals):6d} max {max(vals):6d}  n={len(vals)}")
+    for i in range(1, min(n, 40)):
+        if which == "fwd" and (ev[i][1] >= 20 or ev[i - 1][1] >= 20):
+            print(f"   one-off {ev[i - 1][1]:3d} -> {ev[i][1]:3d}: {ev[i][0] - ev[i - 1][0]}")
     first = ev[0][1]
     idx = [t for t, e in ev if e == first]
     if len(idx) > 4:
