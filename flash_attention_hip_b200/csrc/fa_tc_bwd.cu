@@ -400,22 +400,32 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // block, so each lane draws the 16 bytes of ONE query row and the rows are exchanged.
       uint32_t keep_lo = 0xffffffffu, keep_hi = 0xffffffffu;
       if constexpr (kDropout) {
-        keep_lo = keep_hi = 0;
         const uint32_t bh = (uint32_t)(bidx * a.h + hq);
+        uint32_t w01 = 0, w23 = 0;        // bit 16*b + k: keep(query q_base + 16*b' + lane%16, key k of my block)
 #pragma unroll
         for (int blk = 0; blk < 4; ++blk) {
           const fa_philox4_t rnd = fa_philox4x32((uint32_t)(q_base + blk * 16 + (lane & 15)),
                                                  (uint32_t)(n_abs >> 4), bh, a.ctr3, a.key0, a.key1);
           const uint32_t mine = keep_bits16(rnd, add7, t_msb);
-          uint32_t bits = 0;
-#pragma unroll
-          for (int t = 0; t < 16; ++t) {
-            const uint32_t m = __shfl_sync(0xffffffffu, mine, (lane & 16) | t);
-            bits |= ((m >> (lane & 15)) & 1u) << t;
-          }
-          if (blk < 2) keep_lo |= bits << (16 * blk);
-          else keep_hi |= bits << (16 * (blk - 2));
+          if (blk < 2) w01 |= mine << (16 * blk);
+          else w23 |= mine << (16 * (blk - 2));
         }
+        // 16x16 bit transposes inside each half-warp (four at once, two per word): butterfly over
+        // lane bits 8, 4, 2, 1 -- 8 shuffles instead of the 64 a gather per (query, key) pair costs
+#pragma unroll
+        for (int sft = 8; sft >= 1; sft >>= 1) {
+          const uint32_t m = sft == 8 ? 0x00ff00ffu : sft == 4 ? 0x0f0f0f0fu : sft == 2 ? 0x33333333u : 0x55555555u;
+          const bool lower = (lane & sft) == 0;
+          const uint32_t km = lower ? m : ~m;
+          const uint32_t y01 = __shfl_xor_sync(0xffffffffu, w01, sft);
+          const uint32_t y23 = __shfl_xor_sync(0xffffffffu, w23, sft);
+          const uint32_t z01 = lower ? (y01 << sft) : (y01 >> sft);
+          const uint32_t z23 = lower ? (y23 << sft) : (y23 >> sft);
+          w01 = (w01 & km) | (z01 & ~km);
+          w23 = (w23 & km) | (z23 & ~km);
+        }
+        keep_lo = w01;                    // bit t: keep(query q_base + t, my key)
+        keep_hi = w23;
       }
 
       ptx::mbar_wait(B.q_full + 8 * s, (it >> 1) & 1);   // LSE / D staged
