@@ -215,3 +215,53 @@ def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seql
                                      _stream_ptr(stream), seed, offset, None, None)
     _check(ok, "flash_attn_varlen_bwd")
     return dq, dk, dv
+
+
+# ---- extensions beside the reference ABI (include/flash_attn_b200_ext.h) ---------------------
+
+def set_batch_base(batch_base: int) -> None:
+    """Global index of local batch 0 (keeps dropout masks identical under batch sharding)."""
+    lib().flash_attn_b200_set_batch_base(int(batch_base))
+
+
+_i64 = ctypes.c_int64
+
+
+def _ext(name, argtypes):
+    fn = getattr(lib(), name)
+    fn.argtypes = argtypes
+    fn.restype = ctypes.c_bool
+    return fn
+
+
+def cp_merge(o_acc: torch.Tensor, lse_acc: torch.Tensor, o_blk: torch.Tensor, lse_blk: torch.Tensor,
+             stream: Optional[torch.cuda.Stream] = None) -> None:
+    """Ring step merge.  o_acc fp32 [rows, h, d] (contiguous view), lse_acc fp32 [h, rows] view whose
+    last dim is contiguous (row stride = lse_acc.stride(0)); o_blk 16-bit [rows, h, d]; lse_blk fp32
+    [h, rows].  lse == +inf marks an empty row."""
+    rows, h, d = o_acc.shape
+    assert o_acc.dtype == torch.float32 and o_acc.is_contiguous() and o_blk.is_contiguous()
+    assert o_blk.shape == o_acc.shape and lse_acc.shape == (h, rows) and lse_blk.shape == (h, rows)
+    assert lse_acc.stride(1) == 1 and lse_blk.stride(1) == 1
+    fn = _ext("flash_attn_b200_cp_merge", [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i64, _b, _vp])
+    ok = fn(_ptr(o_acc), _ptr(lse_acc), _ptr(o_blk), _ptr(lse_blk), rows, h, d, lse_acc.stride(0),
+            lse_blk.stride(0), o_blk.dtype == torch.bfloat16, _stream_ptr(stream))
+    _check(ok, "flash_attn_b200_cp_merge")
+
+
+def cp_accumulate(acc: torch.Tensor, blk: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> None:
+    """acc (fp32, contiguous) += blk (fp16/bf16, contiguous, same element count)."""
+    assert acc.dtype == torch.float32 and acc.is_contiguous() and blk.is_contiguous()
+    assert acc.numel() == blk.numel()
+    fn = _ext("flash_attn_b200_cp_accumulate", [_vp, _vp, _i64, _b, _vp])
+    _check(fn(_ptr(acc), _ptr(blk), acc.numel(), blk.dtype == torch.bfloat16, _stream_ptr(stream)),
+           "flash_attn_b200_cp_accumulate")
+
+
+def cp_store(dst: torch.Tensor, src: torch.Tensor, stream: Optional[torch.cuda.Stream] = None) -> None:
+    """dst (fp16/bf16, contiguous) = src (fp32, contiguous)."""
+    assert src.dtype == torch.float32 and src.is_contiguous() and dst.is_contiguous()
+    assert dst.numel() == src.numel()
+    fn = _ext("flash_attn_b200_cp_store", [_vp, _vp, _i64, _b, _vp])
+    _check(fn(_ptr(dst), _ptr(src), src.numel(), dst.dtype == torch.bfloat16, _stream_ptr(stream)),
+           "flash_attn_b200_cp_store")

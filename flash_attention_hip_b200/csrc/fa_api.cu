@@ -19,6 +19,7 @@ thread_local std::string g_error;
 thread_local int g_path_request = FA_B200_PATH_AUTO;
 thread_local int g_last_path = 0;
 thread_local int g_last_launches = 0;
+thread_local int g_batch_base = 0;
 
 bool fail(const char *fmt, ...) __attribute__((format(printf, 1, 2)));
 bool fail(const char *fmt, ...) {
@@ -63,6 +64,7 @@ bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout,
   p.p_dropout = p_dropout;
   p.rp_dropout = fa_dropout_rescale(p_dropout);
   p.drop_threshold = fa_dropout_threshold(p_dropout);
+  p.batch_base = g_batch_base;
   p.seed = seed; p.offset = offset;
   p.causal = is_causal; p.is_bf16 = is_bf16;
   p.cu_q = varlen ? cu_q : nullptr;
@@ -275,10 +277,32 @@ const char *flash_attn_error(void) { return g_error.c_str(); }
 
 void flash_attn_b200_set_path(int path) { g_path_request = path; }
 int flash_attn_b200_last_path(void) { return g_last_path; }
+void flash_attn_b200_set_batch_base(int batch_base) { g_batch_base = batch_base; }
 int flash_attn_b200_last_launch_count(void) { return g_last_launches; }
 int flash_attn_b200_trace_read(int kernel, int role, unsigned long long *dst, int max_events) {
   return kernel == 0 ? fa::trace_read_fwd(dst, role, max_events) : fa::trace_read_bwd(dst, role, max_events);
 }
+// ---- ring context-parallel helpers (include/flash_attn_b200_ext.h; csrc/fa_cp.cu) ----------------
+bool flash_attn_b200_cp_merge(void *o_acc, void *lse_acc, const void *o_blk, const void *lse_blk, int rows,
+                              int num_heads, int head_size, int64_t lse_acc_stride, int64_t lse_blk_stride,
+                              bool is_bf16, fa_stream_t stream) {
+  if (!o_acc || !lse_acc || !o_blk || !lse_blk) return fail("flash_attn_b200_cp_merge: null pointer");
+  if (rows < 0 || num_heads <= 0 || head_size <= 0) return fail("flash_attn_b200_cp_merge: bad shape");
+  const char *e = fa::launch_cp_merge(o_acc, lse_acc, o_blk, lse_blk, rows, num_heads, head_size, lse_acc_stride,
+                                      lse_blk_stride, is_bf16, reinterpret_cast<cudaStream_t>(stream));
+  return e ? fail("flash_attn_b200_cp_merge: %s", e) : true;
+}
+bool flash_attn_b200_cp_accumulate(void *acc_f32, const void *blk, int64_t n, bool is_bf16, fa_stream_t stream) {
+  if (!acc_f32 || !blk || n < 0) return fail("flash_attn_b200_cp_accumulate: bad argument");
+  const char *e = fa::launch_cp_accumulate(acc_f32, blk, n, is_bf16, reinterpret_cast<cudaStream_t>(stream));
+  return e ? fail("flash_attn_b200_cp_accumulate: %s", e) : true;
+}
+bool flash_attn_b200_cp_store(void *dst, const void *src_f32, int64_t n, bool is_bf16, fa_stream_t stream) {
+  if (!dst || !src_f32 || n < 0) return fail("flash_attn_b200_cp_store: bad argument");
+  const char *e = fa::launch_cp_store(dst, src_f32, n, is_bf16, reinterpret_cast<cudaStream_t>(stream));
+  return e ? fail("flash_attn_b200_cp_store: %s", e) : true;
+}
+
 const char *flash_attn_b200_version(void) { return "flash_attn_b200 0.1 (sm_100a)"; }
 
 }  // extern "C"

@@ -38,6 +38,7 @@ struct Params {
   float rp_dropout;    // 1/(1-p)
   uint32_t drop_threshold;  // keep iff byte < threshold
   uint64_t seed, offset;
+  int batch_base;      // global index of local batch 0 (Philox head word; flash_attn_b200_set_batch_base)
   bool causal, is_bf16, deterministic;
 };
 
@@ -93,6 +94,13 @@ bool tc_fwd_supported(const Params &p);
 const char *launch_tc_fwd(const Params &p, cudaStream_t stream);
 bool tc_bwd_supported(const Params &p);
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream);
+
+// Ring context-parallel combine kernels (fa_cp.cu).
+const char *launch_cp_merge(void *o_acc, void *lse_acc, const void *o_blk, const void *lse_blk, int rows, int h,
+                            int d, int64_t lse_acc_stride, int64_t lse_blk_stride, bool is_bf16,
+                            cudaStream_t stream);
+const char *launch_cp_accumulate(void *acc, const void *blk, int64_t n, bool is_bf16, cudaStream_t stream);
+const char *launch_cp_store(void *dst, const void *src, int64_t n, bool is_bf16, cudaStream_t stream);
 
 // Event timelines of a -DFA_TRACE build (0 events otherwise); see fa_trace.cuh.
 int trace_read_bwd(unsigned long long *dst, int role, int max_events);

@@ -87,7 +87,7 @@ generic_bwd_dq_kernel(const Params p) {
 
   const float lse = p.lse[((size_t)b * p.h + h) * p.sq + row];
   const float D = p.softmax_d[((size_t)b * p.h + h) * p.sq_rounded + row];
-  const uint32_t bh = (uint32_t)(b * p.h + h);
+  const uint32_t bh = (uint32_t)((p.batch_base + b) * p.h + h);
   const bool drop = p.p_dropout > 0.f;
   float acc[kMaxD / 32];
 #pragma unroll
@@ -158,7 +158,7 @@ generic_bwd_dkdv_kernel(const Params p) {
     const T *gbase = static_cast<const T *>(p.dout) + ((size_t)si.q0 * p.h + h) * d;
     const float *lse = p.lse + ((size_t)b * p.h + h) * p.sq;
     const float *Dv = p.softmax_d + ((size_t)b * p.h + h) * p.sq_rounded;
-    const uint32_t bh = (uint32_t)(b * p.h + h);
+    const uint32_t bh = (uint32_t)((p.batch_base + b) * p.h + h);
     const T *bias = nullptr;
     if (p.mask) {
       const int64_t bi = p.mask_b == 1 ? 0 : b, hi = p.mask_h == 1 ? 0 : h;

@@ -59,7 +59,7 @@ generic_fwd_kernel(const Params p) {
   if (p.causal) nvis = min(si.sk, row + si.sk - si.sq + 1);
   if (nvis < 0) nvis = 0;
 
-  const uint32_t bh = (uint32_t)(b * p.h + h);
+  const uint32_t bh = (uint32_t)((p.batch_base + b) * p.h + h);
   const bool drop = p.p_dropout > 0.f;
   float m = -INFINITY, l = 0.f;
   float o[kMaxD / 32];

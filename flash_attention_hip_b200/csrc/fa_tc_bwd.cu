@@ -59,7 +59,7 @@ struct BwdArgs {
   float *dq_accum;
   const float *lse, *softmax_d;
   const int32_t *cu_q, *cu_k;
-  int b, sq, sk, sq_rounded, h, hk, nqt;   // sq/sk/nqt: dense values or packed maxima
+  int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
@@ -400,7 +400,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // block, so each lane draws the 16 bytes of ONE query row and the rows are exchanged.
       uint32_t keep_lo = 0xffffffffu, keep_hi = 0xffffffffu;
       if constexpr (kDropout) {
-        const uint32_t bh = (uint32_t)(bidx * a.h + hq);
+        const uint32_t bh = (uint32_t)((a.batch_base + bidx) * a.h + hq);
         uint32_t w01 = 0, w23 = 0;        // bit 16*b + k: keep(query q_base + 16*b' + lane%16, key k of my block)
 #pragma unroll
         for (int blk = 0; blk < 4; ++blk) {
@@ -619,6 +619,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.cu_q = p.cu_q; a.cu_k = p.cu_k;
   a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.sq_rounded = p.sq_rounded; a.h = p.h; a.hk = p.hk;
   a.nqt = (p.sq + kT - 1) / kT;
+  a.batch_base = p.batch_base;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);

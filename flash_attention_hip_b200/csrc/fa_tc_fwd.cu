@@ -102,7 +102,7 @@ struct TcFwdArgs {
   void *out;
   float *lse;
   const int32_t *cu_q, *cu_k;
-  int b, sq, sk, h, hk;
+  int b, sq, sk, h, hk, batch_base;
   float scale_log2;      // softmax_scale * log2(e)
   float rp_dropout;
   uint32_t drop_threshold;
@@ -337,7 +337,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if constexpr (kDropout) {
       dc.add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
       dc.t_msb = a.drop_threshold >= 128u;
-      bh = (uint32_t)(bidx * a.h + head);
+      bh = (uint32_t)((a.batch_base + bidx) * a.h + head);
     }
 
     float m_run = -INFINITY, l_run = 0.f;
@@ -544,7 +544,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
 
   TcFwdArgs a;
   a.out = p.out; a.lse = p.lse; a.cu_q = p.cu_q; a.cu_k = p.cu_k;
-  a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk;
+  a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk; a.batch_base = p.batch_base;
   a.scale_log2 = p.scale * kLog2e;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;

@@ -1,0 +1,150 @@
+"""Ring context parallelism for sequences too long for one GPU (BASELINE.json config 5).
+
+The only exchange step in the project.  The sequence is split over the N ranks of one NVLink box;
+K/V chunks travel round a ring (torch.distributed P2P: NCCL over NVLink on GPUs, gloo in the CPU
+tests) while each rank runs the ORDINARY flash_attn_fwd / flash_attn_bwd entry points
+(/root/reference/flash_attn.h:10-36, :68-99) on (query slice, visiting K/V chunk) pairs.  The
+exchange of step t+1 is issued before the kernels of step t, so it overlaps them.  Per-step results
+are combined by the HBM-bound kernels of csrc/fa_cp.cu.
+
+Causal attention uses zig-zag sharding: the sequence is cut into 2N chunks and rank r holds chunks
+r and 2N-1-r, which balances the triangular work.  With that layout every ring step is one of
+three dense calls (c = chunk length, src = owner of the visiting K/V):
+  src == r : causal,      q[0:2c] x kv[0:2c]
+  src <  r : non-causal,  q[0:2c] x kv[0:c]      (the visitor's late chunk is invisible)
+  src >  r : non-causal,  q[c:2c] x kv[0:2c]     (only the late query chunk sees the visitor)
+Non-causal attention takes any contiguous sharding and calls q x kv non-causally every step.
+
+Dropout is not offered here (its stream is indexed by local coordinates); p_dropout must be 0.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .shard import CudaOps
+
+
+# ---- zig-zag layout helpers (used by callers, the bench and the tests) -------------------------
+
+def zigzag_shard(x: torch.Tensor, rank: int, world_size: int, dim: int = 1) -> torch.Tensor:
+    """Rank `rank`'s zig-zag shard of a full-sequence tensor: chunks rank and 2N-1-rank along `dim`."""
+    chunks = x.chunk(2 * world_size, dim=dim)
+    if len(chunks) != 2 * world_size or any(c.shape[dim] != chunks[0].shape[dim] for c in chunks):
+        raise ValueError("sequence length must be a multiple of 2 * world_size")
+    return torch.cat([chunks[rank], chunks[2 * world_size - 1 - rank]], dim=dim).contiguous()
+
+
+def zigzag_unshard(shards: List[torch.Tensor], dim: int = 1) -> torch.Tensor:
+    """Inverse of zigzag_shard over the list of all ranks' shards."""
+    n = len(shards)
+    chunks = [None] * (2 * n)
+    for r, s in enumerate(shards):
+        a, b = s.chunk(2, dim=dim)
+        chunks[r], chunks[2 * n - 1 - r] = a, b
+    return torch.cat(chunks, dim=dim)
+
+
+def _exchange(send: torch.Tensor, recv: torch.Tensor, group) -> list:
+    """send -> next rank, recv <- previous rank; returns the requests to wait on."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    nxt = dist.get_global_rank(group, (rank + 1) % world) if group is not None else (rank + 1) % world
+    prv = dist.get_global_rank(group, (rank - 1) % world) if group is not None else (rank - 1) % world
+    ops = [dist.P2POp(dist.isend, send, nxt, group), dist.P2POp(dist.irecv, recv, prv, group)]
+    if rank % 2:                      # pairwise-ordered for backends that match P2P ops in issue order
+        ops.reverse()
+    return dist.batch_isend_irecv(ops)
+
+
+def _wait(reqs) -> None:
+    for r in reqs:
+        r.wait()
+
+
+def _steps(causal: bool, rank: int, src: int, s_local: int):
+    """(q rows, kv rows, causal flag) of one ring step; row ranges are (start, stop) in local rows."""
+    if not causal:
+        return (0, s_local), (0, s_local), False
+    c = s_local // 2
+    if src == rank:
+        return (0, s_local), (0, s_local), True
+    if src < rank:
+        return (0, s_local), (0, c), False
+    return (c, s_local), (0, s_local), False
+
+
+def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: bool,
+                  scale: Optional[float] = None, group=None, ops=None):
+    """Forward over the ring.  q [b, s_local, h, d], k/v [b, s_local, hk, d]: this rank's shard
+    (zig-zag when causal).  Returns (out [b, s_local, h, d], lse fp32 [b, h, s_local]) equal to the
+    rank's rows of full-sequence attention."""
+    ops = ops if ops is not None else CudaOps()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    b, s, h, d = q.shape
+    if causal and s % 2:
+        raise ValueError("causal ring attention needs an even local length (zig-zag chunks)")
+    scale = float(d) ** -0.5 if scale is None else scale
+    o_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
+    lse_acc = torch.full((b, h, s), float("inf"), dtype=torch.float32, device=q.device)
+    kv_cur = torch.stack([k, v]).contiguous()
+    kv_nxt = torch.empty_like(kv_cur)
+    for t in range(world):
+        reqs = _exchange(kv_cur, kv_nxt, group) if t + 1 < world else []
+        src = (rank - t) % world
+        (q0, q1), (k0, k1), step_causal = _steps(causal, rank, src, s)
+        for bi in range(b):
+            o_blk, lse_blk = ops.fwd(q[bi:bi + 1, q0:q1], kv_cur[0, bi:bi + 1, k0:k1], kv_cur[1, bi:bi + 1, k0:k1],
+                                     causal=step_causal, scale=scale)
+            ops.merge(o_acc[bi, q0:q1], lse_acc[bi, :, q0:q1], o_blk[0], lse_blk[0])
+        _wait(reqs)
+        kv_cur, kv_nxt = kv_nxt, kv_cur
+    out = torch.empty_like(q)
+    ops.store(out, o_acc)
+    return out, lse_acc
+
+
+def ring_attn_bwd(dout: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor,
+                  lse: torch.Tensor, *, causal: bool, scale: Optional[float] = None, group=None, ops=None):
+    """Backward over the ring from the forward's (out, lse).  The dK/dV partial sums travel with
+    their K/V chunk (fp32) and arrive home after the last hop.  Returns (dq, dk, dv)."""
+    ops = ops if ops is not None else CudaOps()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    b, s, h, d = q.shape
+    scale = float(d) ** -0.5 if scale is None else scale
+    dq_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
+    kv_cur = torch.stack([k, v]).contiguous()
+    kv_nxt = torch.empty_like(kv_cur)
+    dkv_cur = torch.zeros(kv_cur.shape, dtype=torch.float32, device=q.device)
+    dkv_nxt = torch.empty_like(dkv_cur)
+    dkv_reqs: list = []
+    for t in range(world):
+        kv_reqs = _exchange(kv_cur, kv_nxt, group) if t + 1 < world else []
+        src = (rank - t) % world
+        (q0, q1), (k0, k1), step_causal = _steps(causal, rank, src, s)
+        blocks = []
+        for bi in range(b):
+            lse_b = lse[bi:bi + 1, :, q0:q1].contiguous()
+            blocks.append(ops.bwd(dout[bi:bi + 1, q0:q1], q[bi:bi + 1, q0:q1], kv_cur[0, bi:bi + 1, k0:k1],
+                                  kv_cur[1, bi:bi + 1, k0:k1], out[bi:bi + 1, q0:q1], lse_b,
+                                  causal=step_causal, scale=scale))
+        if t > 0:                     # partial sums for the chunk held now arrive from the previous rank
+            _wait(dkv_reqs)
+            dkv_cur, dkv_nxt = dkv_nxt, dkv_cur
+        for bi, (dq_b, dk_b, dv_b) in enumerate(blocks):
+            ops.accumulate(dq_acc[bi, q0:q1], dq_b[0])
+            ops.accumulate(dkv_cur[0, bi, k0:k1], dk_b[0])
+            ops.accumulate(dkv_cur[1, bi, k0:k1], dv_b[0])
+        if world > 1:                 # pass them on; after the last step this hop is the way home
+            dkv_reqs = _exchange(dkv_cur, dkv_nxt, group)
+        _wait(kv_reqs)
+        kv_cur, kv_nxt = kv_nxt, kv_cur
+    if world > 1:
+        _wait(dkv_reqs)
+        dkv_cur = dkv_nxt
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    ops.store(dq, dq_acc)
+    ops.store(dk, dkv_cur[0].contiguous())
+    ops.store(dv, dkv_cur[1].contiguous())
+    return dq, dk, dv

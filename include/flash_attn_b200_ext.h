@@ -31,8 +31,29 @@ void flash_attn_b200_set_path(int path);
  * (FA_B200_PATH_GENERIC or FA_B200_PATH_TCGEN05; 0 before any call). */
 int flash_attn_b200_last_path(void);
 
+/* Batch sharding: the dropout stream is indexed by (batch, head, row, column); a rank
+ * that holds batches [base, base + n) of a global batch sets `batch_base = base` so that its masks
+ * equal the unsharded call's.  Thread-local, sticky, default 0. */
+void flash_attn_b200_set_batch_base(int batch_base);
+
 /* Number of kernel launches the last successful call on this thread enqueued. */
 int flash_attn_b200_last_launch_count(void);
+
+/* ---- ring context parallel (BASELINE.json config 5) -------------------------------------------
+ * Every ring step is an ordinary flash_attn_fwd / flash_attn_bwd call on a (query slice, visiting
+ * K/V chunk) pair; these HBM-bound helpers combine the per-step results.  All pointers are device
+ * memory, all work is enqueued on `stream`; false + flash_attn_error() on failure.
+ *
+ * cp_merge: (o_acc fp32 [rows, h, d], lse_acc fp32, element (head, row) at head*lse_acc_stride+row)
+ *   <- log-sum-exp merge with one step's (o_blk 16-bit [rows, h, d], lse_blk fp32, stride
+ *   lse_blk_stride).  lse == +inf marks a row that has seen no key yet (initialise lse_acc so). */
+bool flash_attn_b200_cp_merge(void *o_acc, void *lse_acc, const void *o_blk, const void *lse_blk, int rows,
+                              int num_heads, int head_size, int64_t lse_acc_stride, int64_t lse_blk_stride,
+                              bool is_bf16, fa_stream_t stream);
+/* acc_f32[i] += blk[i] (16-bit), i < n: dq / dk / dv partial sums of the ring backward. */
+bool flash_attn_b200_cp_accumulate(void *acc_f32, const void *blk, int64_t n, bool is_bf16, fa_stream_t stream);
+/* dst[i] (16-bit) = src_f32[i], i < n. */
+bool flash_attn_b200_cp_store(void *dst, const void *src_f32, int64_t n, bool is_bf16, fa_stream_t stream);
 
 /* Developer builds only (-DFA_TRACE): copies the in-kernel event timeline of warp role `role`
  * of the forward (kernel 0) or backward (kernel 1) tcgen05 kernel's traced CTA into dst as

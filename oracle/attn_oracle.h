@@ -55,6 +55,7 @@ typedef struct {
   const int32_t *cu_seqlens_k;
   const uint16_t *attn_mask;     /* additive bias, storage dtype, or NULL */
   int64_t mask_dims[4];          /* {b|1, h|1, sq, sk} */
+  int32_t batch_base;            /* global index of batch 0 (dropout stream of a batch shard) */
 } fa_oracle_params;
 
 /* Forward.  out: storage dtype, same layout as q.  lse: fp32 [b,h,seqlen_q].

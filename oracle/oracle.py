@@ -41,6 +41,7 @@ class _Params(ctypes.Structure):
         ("cu_seqlens_k", ctypes.c_void_p),
         ("attn_mask", ctypes.c_void_p),
         ("mask_dims", ctypes.c_int64 * 4),
+        ("batch_base", ctypes.c_int32),
     ]
 
 
@@ -116,6 +117,7 @@ class Problem:
     cu_seqlens_k: Optional[np.ndarray] = None
     attn_mask: Optional[np.ndarray] = None      # uint16 storage [mb, mh, sq, sk]
     use_fp64: bool = False
+    batch_base: int = 0      # global index of batch 0 when this problem is a batch shard
 
     def __post_init__(self):
         if self.softmax_scale is None:
@@ -158,6 +160,7 @@ class Problem:
         p.seqlen_q_rounded, p.seqlen_k_rounded = self.seqlen_q_rounded, self.seqlen_k_rounded
         p.p_dropout, p.softmax_scale = self.p_dropout, self.softmax_scale
         p.seed, p.offset = self.seed, self.offset
+        p.batch_base = self.batch_base
         if self.varlen:
             p.cu_seqlens_q = self.cu_seqlens_q.ctypes.data
             p.cu_seqlens_k = self.cu_seqlens_k.ctypes.data
