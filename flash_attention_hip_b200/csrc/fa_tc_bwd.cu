@@ -29,6 +29,9 @@ namespace fa {
 
 namespace {
 
+#ifndef FA_BWD_DRAIN_REGS
+#define FA_BWD_DRAIN_REGS 144
+#endif
 constexpr int kT = 128;            // tile edge: keys per CTA tile, queries per inner tile
 constexpr int kThreads = 512;
 constexpr int kMmaWarp = 8, kLoadWarp = 9, kDrainWarp0 = 12;
@@ -105,6 +108,21 @@ __device__ __forceinline__ uint32_t keep_bits16(const fa_philox4_t &r, uint32_t 
   return bits;
 }
 
+// One butterfly stage of four 16x16 bit transposes (two per word) across the lanes of each
+// half-warp: lanes whose bit kS differs exchange the off-diagonal kS-wide blocks.
+template <int kS>
+__device__ __forceinline__ void bit_transpose_stage(uint32_t &w01, uint32_t &w23, int lane) {
+  constexpr uint32_t m = kS == 8 ? 0x00ff00ffu : kS == 4 ? 0x0f0f0f0fu : kS == 2 ? 0x33333333u : 0x55555555u;
+  const bool lower = (lane & kS) == 0;
+  const uint32_t km = lower ? m : ~m;
+  const uint32_t y01 = __shfl_xor_sync(0xffffffffu, w01, kS);
+  const uint32_t y23 = __shfl_xor_sync(0xffffffffu, w23, kS);
+  const uint32_t z01 = lower ? (y01 << kS) : (y01 >> kS);
+  const uint32_t z23 = lower ? (y23 << kS) : (y23 >> kS);
+  w01 = (w01 & km) | (z01 & ~km);
+  w23 = (w23 & km) | (z23 & ~km);
+}
+
 }  // namespace
 
 namespace {
@@ -122,7 +140,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   using C = Cfg<D>;
   // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
   // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
-  constexpr bool kEarlyDrain = !kDropout;
+  constexpr bool kEarlyDrain = true;
+  // drain / compute registers per thread; 4 x 32 (producers) + 4 x drain + 8 x compute = 2048
+  constexpr int kDrainRegs = D == 64 ? 128 : (kDropout ? FA_BWD_DRAIN_REGS : 208);
+  constexpr int kComputeRegs = (2048 - 128 - 4 * kDrainRegs) / 8;
+  static_assert(kComputeRegs % 8 == 0 && kDrainRegs % 8 == 0, "setmaxnreg takes multiples of 8");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t sbase = ptx::smem_u32(smem_raw);
   if (sbase & 1023u) __trap();   // the swizzled tiles need a 1024-byte aligned base
@@ -318,8 +340,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // =========================== dQ drain warpgroup ======================================
     // register split (16 warps x 128 = 2048 per lane): without dropout the drain warps hold a whole
     // dQ tile (208), with dropout the compute warps need the room for the keep-bit exchange
-    if constexpr (!kEarlyDrain) ptx::setmaxnreg_dec<80>();
-    else ptx::setmaxnreg_inc<D == 128 ? 208 : 128>();
+    if constexpr (kDrainRegs < 128) ptx::setmaxnreg_dec<kDrainRegs>();
+    else ptx::setmaxnreg_inc<kDrainRegs>();
     const int dw = warp - kDrainWarp0;                 // == warp % 4: TMEM lane quadrant
     const int r = dw * 32 + lane;                      // query row inside the tile == TMEM lane
     const uint32_t lane_sel = (uint32_t)(dw * 32) << 16;
@@ -372,8 +394,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (leader) ptx::tma_store_wait<0>();
   } else {
     // =========================== compute warps ============================================
-    if constexpr (!kEarlyDrain) ptx::setmaxnreg_inc<200>();
-    else ptx::setmaxnreg_inc<D == 128 ? 136 : 176>();
+    ptx::setmaxnreg_inc<kComputeRegs>();
     const int w = warp >> 2;                           // which 64 query columns
     const int n = (warp & 3) * 32 + lane;              // key row inside the tile == TMEM lane
     const int n_abs = j * kT + n;
@@ -412,18 +433,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         // 16x16 bit transposes inside each half-warp (four at once, two per word): butterfly over
         // lane bits 8, 4, 2, 1 -- 8 shuffles instead of the 64 a gather per (query, key) pair costs
-#pragma unroll
-        for (int sft = 8; sft >= 1; sft >>= 1) {
-          const uint32_t m = sft == 8 ? 0x00ff00ffu : sft == 4 ? 0x0f0f0f0fu : sft == 2 ? 0x33333333u : 0x55555555u;
-          const bool lower = (lane & sft) == 0;
-          const uint32_t km = lower ? m : ~m;
-          const uint32_t y01 = __shfl_xor_sync(0xffffffffu, w01, sft);
-          const uint32_t y23 = __shfl_xor_sync(0xffffffffu, w23, sft);
-          const uint32_t z01 = lower ? (y01 << sft) : (y01 >> sft);
-          const uint32_t z23 = lower ? (y23 << sft) : (y23 >> sft);
-          w01 = (w01 & km) | (z01 & ~km);
-          w23 = (w23 & km) | (z23 & ~km);
-        }
+        bit_transpose_stage<8>(w01, w23, lane);
+        bit_transpose_stage<4>(w01, w23, lane);
+        bit_transpose_stage<2>(w01, w23, lane);
+        bit_transpose_stage<1>(w01, w23, lane);
         keep_lo = w01;                    // bit t: keep(query q_base + t, my key)
         keep_hi = w23;
       }

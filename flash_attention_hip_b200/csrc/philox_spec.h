@@ -40,7 +40,9 @@
 #define FA_PHILOX_M1 0xCD9E8D57u
 #define FA_PHILOX_W0 0x9E3779B9u
 #define FA_PHILOX_W1 0xBB67AE85u
+#ifndef FA_PHILOX_ROUNDS
 #define FA_PHILOX_ROUNDS 10
+#endif
 #define FA_DROPOUT_COLS_PER_CALL 16
 
 typedef struct { uint32_t v[4]; } fa_philox4_t;
