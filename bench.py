@@ -46,6 +46,17 @@ def load_peaks():
     return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def load_traffic():
+    """DRAM bytes per launch of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum) from the
+    committed ncu --set full capture of this workload (profiles/roofline_traffic.json); None if absent."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(path) as fh:
+            return json.load(fh)["tc_bwd_kernel"]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clocks and throttle reasons of one GPU with nvidia-smi while the timed region runs."""
 
@@ -54,19 +65,30 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.stop_flag = index, [], False
+        self.index, self.samples, self.stop_flag, self.proc = index, [], False, None
 
     def run(self):
-        while not self.stop_flag:
+        # one streaming nvidia-smi (a sample every 50 ms) instead of one process per sample
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                if line.strip():
+                    self.samples.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc is not None:
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                self.proc.terminate()
             except Exception:
                 pass
-            time.sleep(0.1)
+        self.join(timeout=2)
 
     def summary(self):
         if not self.samples:
@@ -150,6 +172,7 @@ def run_ours(args, rank, local_rank, world):
     scratch = (torch.empty((B, H, sq_r), dtype=torch.float32, device=dev),
                torch.empty((B, sq_r, H, d_r), dtype=torch.float32, device=dev))
     kw = dict(p_dropout=P_DROP, is_causal=CAUSAL, seed=SEED, offset=OFFSET)
+    api.set_batch_base(rank * B)      # this rank's batches inside the global batch: shard-invariant dropout
     launches = [0]
 
     def fwd():
@@ -204,8 +227,7 @@ def run_ours(args, rank, local_rank, world):
     n_k = max(3, min(args.steps, 10))
     fwd_ms = time_loop(fwd, n_k)
     bwd_ms = time_loop(lambda: bwd(lse), n_k)
-    sampler.stop_flag = True
-    sampler.join(timeout=2)
+    sampler.stop()
     clocks = sampler.summary()
 
     # e2e: host buffers in, host buffers out, copies inside the timed region
@@ -261,7 +283,7 @@ def run_ours(args, rank, local_rank, world):
                          "vs_nominal_2250": value / world / 2250.0, "peaks": peaks["source"]},
         "kernels": {"fwd_ms": fwd_ms, "fwd_tflops": ff / fwd_ms / 1e9, "bwd_ms": bwd_ms, "bwd_tflops": fb / bwd_ms / 1e9},
         "roofline": {"bound": "tensor", "kernel": dom_name, "achieved": achieved, "peak": peaks["sustained"],
-                     "unit": "TFLOP/s", "frac": achieved / peaks["sustained"], "traffic": None,
+                     "unit": "TFLOP/s", "frac": achieved / peaks["sustained"], "traffic": load_traffic(),
                      "peak_kind": "bf16_tflops_sustained, " + peaks["source"]},
         "roofline_fwd": {"bound": "tensor", "achieved": ff / fwd_ms / 1e9, "peak": peaks["sustained"], "unit": "TFLOP/s",
                          "frac": ff / fwd_ms / 1e9 / peaks["sustained"]},

@@ -61,3 +61,33 @@ if __name__ == "__main__" and WHICH in ("all", "bwd"):
     time_bwd(16, 4096, 32, 128, False)
     time_bwd(16, 4096, 32, 64, True)
     time_bwd(4, 8192, 32, 128, True, hk=8)
+
+
+def time_membound(b, sq, sk, h, d, causal=False, iters=50, hk=None):
+    """Short-sequence / decode-like shapes are HBM- or latency-bound: report achieved GB/s on the
+    algorithmic bytes (read Q, K, V; write O, LSE)."""
+    hk = hk or h
+    q = torch.randn(b, sq, h, d, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(b, sk, hk, d, device="cuda", dtype=torch.bfloat16); v = torch.randn_like(k)
+    out = torch.empty_like(q)
+    for _ in range(5):
+        api.flash_attn_fwd(q, k, v, is_causal=causal, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        api.flash_attn_fwd(q, k, v, is_causal=causal, out=out)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    nbytes = 2 * (2 * q.numel() + 2 * k.numel()) + 4 * b * h * sq
+    fl = 4.0 * b * h * sq * sk * d * (0.5 if causal and sq == sk else 1.0)
+    print(f"fwd-membound b{b} sq{sq} sk{sk} h{h}/{hk} d{d} causal={causal} path={api.last_path()}: {ms * 1e3:.1f} us  "
+          f"{nbytes / ms / 1e6:.1f} GB/s  ({fl / ms / 1e9:.1f} TFLOP/s, {nbytes / 1e6:.2f} MB)", flush=True)
+
+
+if __name__ == "__main__" and WHICH in ("all", "mem"):
+    time_membound(1, 128, 128, 4, 64)                 # BASELINE.json config 1
+    time_membound(256, 128, 128, 16, 128)             # many short sequences
+    time_membound(64, 256, 256, 32, 128, causal=True)
+    time_membound(64, 1, 4096, 32, 128, hk=8)         # decode-like: one query row per sequence, GQA
+    time_membound(16, 1, 16384, 32, 128, hk=8)
