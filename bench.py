@@ -62,10 +62,13 @@ class ClockSampler(threading.Thread):
 
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    # Started BEFORE the warm-up (forking nvidia-smi from a process with a CUDA context stalls the
+    # launching thread for tens of ms); only samples read inside [t_begin, t_end] are summarised.
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag, self.proc = index, [], False, None
+        self.t_begin, self.t_end = 0.0, float("inf")
 
     def run(self):
         # one streaming nvidia-smi (a sample every 50 ms) instead of one process per sample
@@ -77,7 +80,7 @@ class ClockSampler(threading.Thread):
                 if self.stop_flag:
                     break
                 if line.strip():
-                    self.samples.append([x.strip() for x in line.split(",")])
+                    self.samples.append([time.time()] + [x.strip() for x in line.split(",")])
         except Exception:
             pass
 
@@ -91,14 +94,15 @@ class ClockSampler(threading.Thread):
         self.join(timeout=2)
 
     def summary(self):
-        if not self.samples:
+        rows = [r[1:] for r in self.samples if self.t_begin - 0.06 <= r[0] <= self.t_end + 0.06]
+        if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        sm = sorted(int(r[0]) for r in rows if r[0].isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None,
-                "sm_max_mhz": int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
-                "reasons": reasons, "samples": len(self.samples)}
+                "sm_max_mhz": int(rows[0][1]) if rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(rows)}
 
 
 def cpu_sample(steps=1, heads=None):
@@ -193,23 +197,26 @@ def run_ours(args, rank, local_rank, world):
             dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    time.sleep(0.3)                   # let the fork finish before anything is timed
+    for _ in range(max(args.warmup, 5)):
         step()
     fwd_path = None
     lse = fwd(); fwd_path = api.last_path()
     bwd(lse); bwd_path = api.last_path()
     sync_all()
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches[0] = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    sampler.t_begin = time.time()
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
     sync_all()
+    sampler.t_end = time.time()
     ms = e0.elapsed_time(e1)
     n_launch = launches[0]
 

@@ -54,6 +54,54 @@ bwd_preprocess_kernel(const Params p) {
   if (lane == 0) p.softmax_d[((size_t)b * p.h + h) * p.sq_rounded + row] = acc;
 }
 
+// Same result for dense inputs whose head_size / 8 is a power of two (64, 128, 256): dout and out are
+// flat [token * heads][d] arrays, so consecutive lanes stream consecutive 16-byte vectors (kLanes per
+// row, four rows in flight per lane) instead of one half-empty warp per row.  HBM-bound: reads dout
+// and out once.
+template <typename T, int kLanes>
+__global__ void __launch_bounds__(256)
+bwd_preprocess_flat_kernel(const T *__restrict__ o, const T *__restrict__ g, float *__restrict__ softmax_d,
+                           long long rows, int h, int sq, int sq_rounded) {
+  constexpr int kUnroll = 4;
+  const long long nvec = rows * kLanes;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  // warp-uniform trip count (the shuffles below need the whole warp)
+  for (long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; v0 - lane < nvec; v0 += stride * kUnroll) {
+    uint4 ro[kUnroll], rg[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      if (v < nvec) {
+        ro[u] = reinterpret_cast<const uint4 *>(o)[v];
+        rg[u] = reinterpret_cast<const uint4 *>(g)[v];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      float acc = 0.f;
+      if (v < nvec) {
+        const T *eo = reinterpret_cast<const T *>(&ro[u]);
+        const T *eg = reinterpret_cast<const T *>(&rg[u]);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc = fmaf(to_f32<T>(eo[t]), to_f32<T>(eg[t]), acc);
+      }
+      // stride is a multiple of 32, so the kLanes lanes of a row stay together in one warp
+#pragma unroll
+      for (int off = kLanes / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+      if (v < nvec && (v % kLanes) == 0) {
+        const long long r = v / kLanes;                  // (token, head) row
+        const long long tok = r / h;
+        const int head = (int)(r % h);
+        const long long b = tok / sq;
+        const int row = (int)(tok % sq);
+        softmax_d[(b * h + head) * sq_rounded + row] = acc;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 generic_bwd_dq_kernel(const Params p) {
@@ -230,6 +278,24 @@ const char *launch_bwd_t(const Params &p, cudaStream_t stream) {
 const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream) {
   if (p.d % 8) return "backward: head_size must be a multiple of 8";
   if (p.b == 0 || p.sq == 0) return nullptr;
+  const int lanes = p.d / 8;
+  if (!p.cu_q && (lanes == 8 || lanes == 16 || lanes == 32)) {
+    const long long rows = (long long)p.b * p.sq * p.h;
+    const long long blocks = (rows * lanes + 256 * 4 - 1) / (256 * 4);
+    const int grid = (int)(blocks < 148 * 8 ? blocks : 148 * 8);      // grid-stride, 8 CTAs per SM
+#define FA_PRE(T, L)                                                                                     \
+  bwd_preprocess_flat_kernel<T, L><<<grid, 256, 0, stream>>>(static_cast<const T *>(p.out),              \
+                                                             static_cast<const T *>(p.dout), p.softmax_d, \
+                                                             rows, p.h, p.sq, p.sq_rounded)
+    if (p.is_bf16) {
+      if (lanes == 8) FA_PRE(__nv_bfloat16, 8); else if (lanes == 16) FA_PRE(__nv_bfloat16, 16); else FA_PRE(__nv_bfloat16, 32);
+    } else {
+      if (lanes == 8) FA_PRE(__half, 8); else if (lanes == 16) FA_PRE(__half, 16); else FA_PRE(__half, 32);
+    }
+#undef FA_PRE
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+  }
   dim3 grid((p.sq + kWarpsPerBlock - 1) / kWarpsPerBlock, p.h, p.b);
   if (p.is_bf16)
     bwd_preprocess_kernel<__nv_bfloat16><<<grid, kWarpsPerBlock * 32, 0, stream>>>(p);
