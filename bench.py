@@ -132,6 +132,8 @@ def cpu_sample(steps=1, heads=None):
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     vals = []
     last = None
     for i in range(args.warmup + args.steps):
