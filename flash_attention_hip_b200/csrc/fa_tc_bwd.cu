@@ -62,7 +62,8 @@ struct BwdArgs {
   float *dq_accum;
   const float *lse, *softmax_d;
   const int32_t *cu_q, *cu_k;
-  int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;   // sq/sk/nqt: dense values or packed maxima
+  int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;
+  int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
@@ -351,7 +352,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = i_min + it % n_i;
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
-      float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * (D / 32)) * 4096;
+      float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * a.nblk) * 4096;
       FA_TRACE_EV(trd, 20);
       ptx::mbar_wait(B.dq_full, it & 1);
       ptx::tc_fence_after();
@@ -367,7 +368,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       FA_TRACE_EV(trd, 22);
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c, ++cc) {
+      for (int c = 0; c < D / 32; ++c) {
+        if (c >= a.nblk) break;                        // head_size < D: the last blocks are all zero
         uint32_t(&vc)[32] = v[kEarlyDrain ? c : 0];
         if constexpr (!kEarlyDrain) {
           ptx::tmem_ld_x32(tDP + lane_sel + c * 32, vc);
@@ -389,6 +391,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           bulk_reduce_add_f32(gdst + c * 4096, buf, 16384);
           ptx::tma_store_commit();
         }
+        ++cc;
       }
     }
     if (leader) ptx::tma_store_wait<0>();
@@ -538,8 +541,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::tc_fence_after();
     constexpr int kHalf = D / 2;                         // columns per warp half
     const size_t tok = ktok0 + n_abs;
-    uint16_t *dkp = static_cast<uint16_t *>(a.dk) + (tok * a.hk + hk) * D + w * kHalf;
-    uint16_t *dvp = static_cast<uint16_t *>(a.dv) + (tok * a.hk + hk) * D + w * kHalf;
+    uint16_t *dkp = static_cast<uint16_t *>(a.dk) + (tok * a.hk + hk) * a.d + w * kHalf;
+    uint16_t *dvp = static_cast<uint16_t *>(a.dv) + (tok * a.hk + hk) * a.d + w * kHalf;
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
       const uint32_t tsrc = (which ? tDK : tDV) + lane_sel + w * kHalf;
@@ -563,7 +566,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             o.y = pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16);
             o.z = pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16);
             o.w = pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16);
-            dst[c * 4 + x] = o;
+            if (w * kHalf + c * 32 + x * 8 < a.d) dst[c * 4 + x] = o;
           }
         }
       }
@@ -587,7 +590,7 @@ namespace {
 template <int D, bool kBF16>
 __global__ void __launch_bounds__(256)
 dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const int32_t *__restrict__ cu_q,
-                  int sq, int h, int nqt, float scale) {
+                  int sq, int h, int nqt, float scale, int d, int nblk) {
   const int i = blockIdx.x, hq = blockIdx.y, bidx = blockIdx.z;
   size_t tok0 = (size_t)bidx * sq;
   if (cu_q) {
@@ -595,8 +598,8 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
     sq = cu_q[bidx + 1] - cu_q[bidx];
     if (i * 128 >= sq) return;
   }
-  const float *src = acc + ((((size_t)bidx * h + hq) * nqt + i) * (D / 32)) * 4096;
-  constexpr int kVecPerRow = D / 8;                    // 16-byte output vectors per row
+  const float *src = acc + ((((size_t)bidx * h + hq) * nqt + i) * nblk) * 4096;
+  const int kVecPerRow = d / 8;                        // 16-byte output vectors per row
   for (int idx = threadIdx.x; idx < 128 * kVecPerRow; idx += 256) {
     const int r = idx / kVecPerRow, vcol = idx % kVecPerRow;
     const int row = i * 128 + r;
@@ -610,7 +613,7 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
     o.y = pack2(x.z * scale, x.w * scale, kBF16);
     o.z = pack2(y.x * scale, y.y * scale, kBF16);
     o.w = pack2(y.z * scale, y.w * scale, kBF16);
-    uint16_t *dst = static_cast<uint16_t *>(dq) + ((tok0 + row) * h + hq) * D + d0;
+    uint16_t *dst = static_cast<uint16_t *>(dq) + ((tok0 + row) * h + hq) * d + d0;
     *reinterpret_cast<uint4 *>(dst) = o;
   }
 }
@@ -622,10 +625,10 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   const char *e;
   // packed: one batch entry whose row count each CTA replaces (ptx::patch_rows)
   const uint64_t nb = p.cu_q ? 1 : (uint64_t)p.b;
-  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, p.sq, nb, kT))) return e;
-  if ((e = make_tmap_rows(&tdo, p.dout, kBF16, D, p.h, p.sq, nb, kT))) return e;
-  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, p.sk, nb, kT))) return e;
-  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, p.sk, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tq, p.q, kBF16, p.d, p.h, p.sq, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tdo, p.dout, kBF16, p.d, p.h, p.sq, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tk, p.k, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tv, p.v, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
 
   BwdArgs a;
   a.dk = p.dk; a.dv = p.dv; a.dq_accum = p.dq_accum; a.lse = p.lse; a.softmax_d = p.softmax_d;
@@ -633,6 +636,8 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.sq_rounded = p.sq_rounded; a.h = p.h; a.hk = p.hk;
   a.nqt = (p.sq + kT - 1) / kT;
   a.batch_base = p.batch_base;
+  a.d = p.d;
+  a.nblk = (p.d + 31) / 32;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
@@ -640,7 +645,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.ctr3 = (uint32_t)p.offset;
   a.causal = p.causal ? 1 : 0;
 
-  const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * D * sizeof(float);
+  const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * a.nblk * 32 * sizeof(float);
   if (cudaMemsetAsync(p.dq_accum, 0, acc_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq_accum) failed";
 
   auto kern = tc_bwd_kernel<D, kBF16, kDropout>;
@@ -655,7 +660,8 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
-  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale);
+  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale, a.d,
+                                                         a.nblk);
   err = cudaGetLastError();
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
 }
@@ -672,14 +678,14 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 }
 
 bool tc_bwd_supported(const Params &p) {
-  if (p.d != 64 && p.d != 128) return false;
+  if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
   if (p.mask) return false;
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
   if (p.deterministic) return false;                  // reduce-add order is not fixed
   if (!p.dq_accum) return false;
   // scratch contract (include/flash_attn.h): dq_accum >= b * sq_rounded * h * d_rounded floats
-  if (p.sq_rounded % kT || p.sq_rounded < p.sq || p.d_rounded < p.d) return false;
+  if (p.sq_rounded % kT || p.sq_rounded < p.sq || p.d_rounded < (p.d + 31) / 32 * 32) return false;
   return true;
 }
 
@@ -689,7 +695,7 @@ const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   if (p.is_bf16) return drop ? launch_tc_bwd_t<DD, true, true>(p, stream)                          \
                              : launch_tc_bwd_t<DD, true, false>(p, stream);                        \
   return drop ? launch_tc_bwd_t<DD, false, true>(p, stream) : launch_tc_bwd_t<DD, false, false>(p, stream);
-  if (p.d == 128) { FA_DISPATCH(128) }
+  if (p.d > 64) { FA_DISPATCH(128) }
   FA_DISPATCH(64)
 #undef FA_DISPATCH
 }

@@ -103,6 +103,7 @@ struct TcFwdArgs {
   float *lse;
   const int32_t *cu_q, *cu_k;
   int b, sq, sk, h, hk, batch_base;
+  int d;                 // real head_size (<= D, multiple of 8); columns [d, D) are TMA zero fill
   float scale_log2;      // softmax_scale * log2(e)
   float rp_dropout;
   uint32_t drop_threshold;
@@ -463,7 +464,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // ---- epilogue: O_t / l -> global, LSE ------------------------------------------
     const bool row_ok = row < sq;
     const size_t tok = (size_t)(a.cu_q ? q0 : bidx * a.sq) + row;
-    uint4 *orow = reinterpret_cast<uint4 *>(static_cast<uint16_t *>(a.out) + (tok * a.h + head) * D);
+    uint4 *orow = reinterpret_cast<uint4 *>(static_cast<uint16_t *>(a.out) + (tok * a.h + head) * a.d);
     if (n_t > 0) {
       ptx::mbar_wait(B.pv_done + 8 * t, (n_t - 1) & 1);
       ptx::tc_fence_after();
@@ -481,13 +482,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             v.y = pack_pair(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv, kBF16);
             v.z = pack_pair(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv, kBF16);
             v.w = pack_pair(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv, kBF16);
-            orow[c * 4 + i] = v;
+            if ((c * 4 + i) * 8 < a.d) orow[c * 4 + i] = v;
           }
         }
       }
     } else if (row_ok) {
 #pragma unroll
-      for (int i = 0; i < D / 8; ++i) orow[i] = make_uint4(0, 0, 0, 0);
+      for (int i = 0; i < D / 8; ++i)
+        if (i * 8 < a.d) orow[i] = make_uint4(0, 0, 0, 0);
     }
     if (row_ok) {
       const float m_use = m_run == -INFINITY ? 0.f : m_run;
@@ -519,7 +521,7 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 }
 
 bool tc_fwd_supported(const Params &p) {
-  if (p.d != 64 && p.d != 128) return false;
+  if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
   if (p.mask || p.softmax_ret) return false;     // bias / S_dmask: all-shapes kernel
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
   if (p.sq <= 0 || p.sk <= 0) return false;
@@ -538,13 +540,14 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   const uint64_t rows_q = (uint64_t)p.sq, rows_k = (uint64_t)p.sk;
   const uint64_t nb = packed ? 1 : (uint64_t)p.b;
   const char *e;
-  if ((e = make_tmap_rows(&tq, p.q, kBF16, D, p.h, rows_q, nb, kTileM))) return e;
-  if ((e = make_tmap_rows(&tk, p.k, kBF16, D, p.hk, rows_k, nb, kTileN))) return e;
-  if ((e = make_tmap_rows(&tv, p.v, kBF16, D, p.hk, rows_k, nb, kTileN))) return e;
+  if ((e = make_tmap_rows(&tq, p.q, kBF16, p.d, p.h, rows_q, nb, kTileM))) return e;
+  if ((e = make_tmap_rows(&tk, p.k, kBF16, p.d, p.hk, rows_k, nb, kTileN))) return e;
+  if ((e = make_tmap_rows(&tv, p.v, kBF16, p.d, p.hk, rows_k, nb, kTileN))) return e;
 
   TcFwdArgs a;
   a.out = p.out; a.lse = p.lse; a.cu_q = p.cu_q; a.cu_k = p.cu_k;
   a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk; a.batch_base = p.batch_base;
+  a.d = p.d;
   a.scale_log2 = p.scale * kLog2e;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
@@ -574,7 +577,7 @@ const char *launch_tc_fwd(const Params &p, cudaStream_t stream) {
   if (p.is_bf16) return drop ? launch_tc_fwd_t<DD, true, true>(p, stream)                        \
                              : launch_tc_fwd_t<DD, true, false>(p, stream);                      \
   return drop ? launch_tc_fwd_t<DD, false, true>(p, stream) : launch_tc_fwd_t<DD, false, false>(p, stream);
-  if (p.d == 128) { FA_DISPATCH(128) }
+  if (p.d > 64) { FA_DISPATCH(128) }
   FA_DISPATCH(64)
 #undef FA_DISPATCH
 }

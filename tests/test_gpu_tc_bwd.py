@@ -27,6 +27,13 @@ CASES = {
     "dropout_d128": lambda: cases.dense(2, 384, 384, 2, 2, 128, is_causal=True, p_dropout=0.1, seed=1234, offset=0),
     "dropout_d64_p50_gqa": lambda: cases.dense(1, 300, 450, 4, 2, 64, p_dropout=0.5, seed=2**40 + 3, offset=2**33 + 9),
     "dropout_p80": lambda: cases.dense(1, 256, 256, 2, 2, 64, p_dropout=0.8, seed=7, offset=1),
+    # head sizes between the two compiled widths ride the 64 / 128 kernels (TMA zero fill)
+    "d96_causal_gqa": lambda: cases.dense(2, 300, 300, 4, 2, 96, is_causal=True),
+    "d80_ragged": lambda: cases.dense(1, 200, 333, 2, 2, 80),
+    "d40_dropout": lambda: cases.dense(1, 257, 257, 2, 2, 40, is_causal=True, p_dropout=0.2, seed=11, offset=4),
+    "d32_fp16": lambda: cases.dense(1, 128, 384, 2, 2, 32, is_bf16=False),
+    "d104_dropout": lambda: cases.dense(1, 384, 384, 2, 1, 104, p_dropout=0.1, seed=5, offset=0),
+    "d8_tiny": lambda: cases.dense(1, 130, 130, 1, 1, 8, is_causal=True),
     "c2_small_b2h4s2048d128": lambda: cases.dense(2, 2048, 2048, 4, 4, 128, is_causal=True, p_dropout=0.1, seed=5),
 }
 

@@ -25,6 +25,8 @@ CASES = {
                                            p_dropout=0.1, seed=1234, offset=7),
     "fp16_dropout": lambda: cases.varlen([250, 250], [250, 250], 2, 1, 64, p_dropout=0.25, seed=3, offset=0,
                                          is_bf16=False),
+    "d96_ragged_causal_gqa": lambda: cases.varlen([200, 77, 300], [200, 77, 300], 4, 2, 96, is_causal=True),
+    "d48_sq_ne_sk": lambda: cases.varlen([100, 300], [260, 128], 2, 2, 48),
     "c4_mix_d128_causal_h8": lambda: cases.varlen(C4_LENS, C4_LENS, 8, 2, 128, is_causal=True),
     "c4_mix_d64_h4": lambda: cases.varlen(C4_LENS[2:], C4_LENS[2:], 4, 1, 64),
 }
