@@ -63,6 +63,8 @@ struct BwdArgs {
   const float *lse, *softmax_d;
   const int32_t *cu_q, *cu_k;
   int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;
+  const void *mask;      // additive bias [mask_b, mask_h, sq, sk] in the input dtype, or null (dense only)
+  int mask_b, mask_h;
   int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
@@ -133,7 +135,7 @@ struct BwdBars {
       dq_full, dq_drained, acc_done;
 };
 
-template <int D, bool kBF16, bool kDropout>
+template <int D, bool kBF16, bool kDropout, bool kMask>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
@@ -459,7 +461,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
       const int lim = n_abs - shift;                     // causal: visible iff q >= lim
-      const float2 c2v = make_float2(c2, c2);
+      float cs = c2;
+      if constexpr (kMask) {                                      // uniform: attn_mask (reference flash_attn.h:98-99)
+        // s <- s * scale_log2 + bias * log2 e; lanes hold consecutive keys, so each load is coalesced
+        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
+            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * sq + q_base) * (size_t)sk + n_abs;
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          float bias = 0.f;
+          if (kv_valid && q_base + c < sq) {
+            const uint16_t mb = mp[(size_t)c * sk];
+            bias = kBF16 ? __uint_as_float((uint32_t)mb << 16) : __half2float(*reinterpret_cast<const __half *>(&mb));
+          }
+          p[c] = fmaf(p[c], c2, bias * kLog2e);
+        }
+        cs = 1.f;
+      }
+      const float2 c2v = make_float2(cs, cs);
 #pragma unroll
       for (int c = 0; c < 64; c += 4) {
         const float4 nl = ld_shared_f32x4(stat + 4 * c);                  // -lse2 of 4 query columns
@@ -618,7 +636,7 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
   }
 }
 
-template <int D, bool kBF16, bool kDropout>
+template <int D, bool kBF16, bool kDropout, bool kMask>
 const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
   CUtensorMap tq, tk, tv, tdo;
@@ -638,6 +656,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.batch_base = p.batch_base;
   a.d = p.d;
   a.nblk = (p.d + 31) / 32;
+  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
@@ -648,7 +667,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * a.nblk * 32 * sizeof(float);
   if (cudaMemsetAsync(p.dq_accum, 0, acc_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq_accum) failed";
 
-  auto kern = tc_bwd_kernel<D, kBF16, kDropout>;
+  auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask>;
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kBytes) != cudaSuccess)
@@ -679,7 +698,7 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
-  if (p.mask) return false;
+  if (p.mask && p.cu_q) return false;
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
   if (p.deterministic) return false;                  // reduce-add order is not fixed
@@ -691,13 +710,15 @@ bool tc_bwd_supported(const Params &p) {
 
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   const bool drop = p.p_dropout > 0.f;
+#define FA_MASKED(DD, BF, DR) (p.mask ? launch_tc_bwd_t<DD, BF, DR, true>(p, stream) : launch_tc_bwd_t<DD, BF, DR, false>(p, stream))
 #define FA_DISPATCH(DD)                                                                          \
-  if (p.is_bf16) return drop ? launch_tc_bwd_t<DD, true, true>(p, stream)                          \
-                             : launch_tc_bwd_t<DD, true, false>(p, stream);                        \
-  return drop ? launch_tc_bwd_t<DD, false, true>(p, stream) : launch_tc_bwd_t<DD, false, false>(p, stream);
+  if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                          \
+                             : FA_MASKED(DD, true, false);                        \
+  return drop ? FA_MASKED(DD, false, true) : FA_MASKED(DD, false, false);
   if (p.d > 64) { FA_DISPATCH(128) }
   FA_DISPATCH(64)
 #undef FA_DISPATCH
+#undef FA_MASKED
 }
 
 }  // namespace fa

@@ -103,6 +103,8 @@ struct TcFwdArgs {
   float *lse;
   const int32_t *cu_q, *cu_k;
   int b, sq, sk, h, hk, batch_base;
+  const void *mask;      // additive bias [mask_b, mask_h, sq, sk] in the input dtype, or null (dense only)
+  int mask_b, mask_h;
   int d;                 // real head_size (<= D, multiple of 8); columns [d, D) are TMA zero fill
   float scale_log2;      // softmax_scale * log2(e)
   float rp_dropout;
@@ -111,7 +113,7 @@ struct TcFwdArgs {
   int causal;
 };
 
-template <int D, bool kBF16, bool kDropout>
+template <int D, bool kBF16, bool kDropout, bool kMask>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const TcFwdArgs a) {
@@ -329,7 +331,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const uint32_t tP = tS + kPOff;
     const uint32_t tO = tmem + 256 + t * 128 + lane_sel;
     const int n_t = ntile[t];
-    const float c2 = a.scale_log2;
+    // with an additive bias the scores are moved to the scaled log2 domain when they are read
+    // (s <- s * scale_log2 + bias * log2 e), and everything after works with a unit scale
+    const float c2 = kMask ? 1.f : a.scale_log2;
+    const uint16_t *mrow = nullptr;
+    if (kMask && row < sq)
+      mrow = static_cast<const uint16_t *>(a.mask) +
+             (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * sq + row) * (size_t)sk;
+    const bool mvec = (sk % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.mask) & 15) == 0);
     const int row_limit = row + shift;                // last visible key when causal
     const int tile_row0 = m0 + t * kTileM;
 
@@ -362,6 +371,26 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       FA_TRACE_EV(trs, 12);
       const int col0 = j * kTileN;
+      if constexpr (kMask) {                                   // uniform: attn_mask (reference flash_attn.h:35-36)
+        const float sc = a.scale_log2;
+#pragma unroll
+        for (int c8 = 0; c8 < kTileN; c8 += 8) {
+          uint16_t mb[8];
+          const int col = col0 + c8;
+          if (mrow && mvec && col + 8 <= sk) {
+            *reinterpret_cast<uint4 *>(mb) = *reinterpret_cast<const uint4 *>(mrow + col);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mb[e] = (mrow && col + e < sk) ? mrow[col + e] : (uint16_t)0;
+          }
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float bias = kBF16 ? __uint_as_float((uint32_t)mb[e] << 16)
+                                     : __half2float(*reinterpret_cast<const __half *>(&mb[e]));
+            s[c8 + e] = __float_as_uint(fmaf(__uint_as_float(s[c8 + e]), sc, bias * kLog2e));
+          }
+        }
+      }
       // masking is needed only on the diagonal and on the ragged last tile (warp-uniform test)
       const bool need_mask = (col0 + kTileN > sk) || (a.causal && col0 + kTileN - 1 > tile_row0 + shift);
       if (need_mask) {
@@ -522,7 +551,8 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_fwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
-  if (p.mask || p.softmax_ret) return false;     // bias / S_dmask: all-shapes kernel
+  if (p.softmax_ret) return false;               // S_dmask output: all-shapes kernel
+  if (p.mask && p.cu_q) return false;
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;
@@ -530,7 +560,7 @@ bool tc_fwd_supported(const Params &p) {
 
 namespace {
 
-template <int D, bool kBF16, bool kDropout>
+template <int D, bool kBF16, bool kDropout, bool kMask>
 const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
   CUtensorMap tq, tk, tv;
@@ -548,6 +578,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.out = p.out; a.lse = p.lse; a.cu_q = p.cu_q; a.cu_k = p.cu_k;
   a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk; a.batch_base = p.batch_base;
   a.d = p.d;
+  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
   a.scale_log2 = p.scale * kLog2e;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
@@ -556,7 +587,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.ctr3 = (uint32_t)p.offset;
   a.causal = p.causal ? 1 : 0;
 
-  auto kern = tc_fwd_kernel<D, kBF16, kDropout>;
+  auto kern = tc_fwd_kernel<D, kBF16, kDropout, kMask>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmemBytes) != cudaSuccess)
@@ -573,13 +604,15 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
 
 const char *launch_tc_fwd(const Params &p, cudaStream_t stream) {
   const bool drop = p.p_dropout > 0.f;
+#define FA_MASKED(DD, BF, DR) (p.mask ? launch_tc_fwd_t<DD, BF, DR, true>(p, stream) : launch_tc_fwd_t<DD, BF, DR, false>(p, stream))
 #define FA_DISPATCH(DD)                                                                        \
-  if (p.is_bf16) return drop ? launch_tc_fwd_t<DD, true, true>(p, stream)                        \
-                             : launch_tc_fwd_t<DD, true, false>(p, stream);                      \
-  return drop ? launch_tc_fwd_t<DD, false, true>(p, stream) : launch_tc_fwd_t<DD, false, false>(p, stream);
+  if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                        \
+                             : FA_MASKED(DD, true, false);                      \
+  return drop ? FA_MASKED(DD, false, true) : FA_MASKED(DD, false, false);
   if (p.d > 64) { FA_DISPATCH(128) }
   FA_DISPATCH(64)
 #undef FA_DISPATCH
+#undef FA_MASKED
 }
 
 }  // namespace fa

@@ -91,3 +91,31 @@ if __name__ == "__main__" and WHICH in ("all", "mem"):
     time_membound(64, 256, 256, 32, 128, causal=True)
     time_membound(64, 1, 4096, 32, 128, hk=8)         # decode-like: one query row per sequence, GQA
     time_membound(16, 1, 16384, 32, 128, hk=8)
+
+
+def time_mask(b, s, h, d, iters=10):
+    """attn_mask path (additive bias [1, 1, s, s] broadcast over batch and heads) on the tcgen05 kernels."""
+    q = torch.randn(b, s, h, d, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn_like(q); v = torch.randn_like(q); do = torch.randn_like(q)
+    mask = torch.randn(1, 1, s, s, device="cuda", dtype=torch.bfloat16)
+    out, lse, _, _ = api.flash_attn_fwd(q, k, v, attn_mask=mask)
+    pf = api.last_path()
+    api.flash_attn_bwd(do, q, k, v, out, lse, attn_mask=mask)
+    pb_ = api.last_path()
+    torch.cuda.synchronize()
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    e[0].record()
+    for _ in range(iters):
+        api.flash_attn_fwd(q, k, v, attn_mask=mask, out=out)
+    e[1].record()
+    for _ in range(iters):
+        api.flash_attn_bwd(do, q, k, v, out, lse, attn_mask=mask)
+    e[2].record(); torch.cuda.synchronize()
+    fl = 4.0 * b * h * s * s * d
+    tf, tb = e[0].elapsed_time(e[1]) / iters, e[1].elapsed_time(e[2]) / iters
+    print(f"attn_mask b{b} s{s} h{h} d{d} paths={pf}/{pb_}: fwd {tf:.3f} ms {fl / tf / 1e9:.1f} TFLOP/s, "
+          f"bwd {tb:.3f} ms {2.5 * fl / tb / 1e9:.1f} TFLOP/s", flush=True)
+
+
+if __name__ == "__main__" and WHICH in ("all", "mask"):
+    time_mask(8, 4096, 32, 128)
