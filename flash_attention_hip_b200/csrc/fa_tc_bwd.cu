@@ -65,6 +65,7 @@ struct BwdArgs {
   int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;
   const void *mask;      // additive bias [mask_b, mask_h, sq, sk] in the input dtype, or null (dense only)
   int mask_b, mask_h;
+  int *sem;              // deterministic dQ (num_splits == 1): one turn counter per (batch, head, query tile)
   int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
@@ -135,7 +136,7 @@ struct BwdBars {
       dq_full, dq_drained, acc_done;
 };
 
-template <int D, bool kBF16, bool kDropout, bool kMask>
+template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
@@ -173,6 +174,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   }
   const int n_i = max(0, nqt - i_min);         // query tiles per head
   const int n_it = n_i * group;                // inner iterations: (head in group, query tile)
+  // Query tile of inner iteration `it`.  Ordered (deterministic) dQ walks the tiles from the last one
+  // down: every key-tile CTA of a causal problem then starts on the same query tile and the turns
+  // form a pipeline, instead of CTA j first waiting for the diagonal tile of all its predecessors.
+  constexpr bool descending = kOrdered;
+  auto q_tile_of = [&](int it) { return descending ? i_min + n_i - 1 - it % n_i : i_min + it % n_i; };
 
   // ---- barriers, tensor memory --------------------------------------------------------
   const uint32_t bar0 = sbase + C::kBar;
@@ -235,7 +241,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
       for (int it = 0; it < n_it; ++it) {
-        const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+        const int hq = hk * group + it / n_i, i = q_tile_of(it);
         const int s = it & 1;
         if (it >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((it >> 1) - 1) & 1);
         if (lane == 0) {
@@ -352,7 +358,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     uint32_t cc = 0;                                   // running 16 KB block counter (staging ring of 2)
     FA_TRACE_DECL(trd, 1, tr_cta && leader);
     for (int it = 0; it < n_it; ++it) {
-      const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+      const int hq = hk * group + it / n_i, i = q_tile_of(it);
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
       float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * a.nblk) * 4096;
       FA_TRACE_EV(trd, 20);
@@ -369,6 +375,21 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::mbar_arrive(B.dq_drained);
       }
       FA_TRACE_EV(trd, 22);
+      // Deterministic dQ: the key tiles add into a query tile in ascending order.  CTA j takes its
+      // turn when the counter reads j (CTAs 0..j-1 of this (batch, kv head) were dispatched before
+      // it, so the wait cannot deadlock) and passes it on once its reduce-adds have completed.
+      int *turn = nullptr;
+      if constexpr (kOrdered) {
+        turn = a.sem + ((size_t)bidx * a.h + hq) * a.nqt + i;
+        if (leader) {
+          const long long t0 = clock64();
+          int seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turn) : "memory");
+            if (clock64() - t0 > (1ll << 32)) __trap();
+          } while (seen != j);
+        }
+      }
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
         if (c >= a.nblk) break;                        // head_size < D: the last blocks are all zero
@@ -395,6 +416,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         ++cc;
       }
+      if (kOrdered && leader) {
+        ptx::tma_store_wait<0>();                      // my adds for this tile have been performed
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(j + 1) : "memory");
+      }
     }
     if (leader) ptx::tma_store_wait<0>();
   } else {
@@ -416,7 +442,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
     FA_TRACE_DECL(trc, 2 + w, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int it = 0; it < n_it; ++it) {
-      const int hq = hk * group + it / n_i, i = i_min + it % n_i;
+      const int hq = hk * group + it / n_i, i = q_tile_of(it);
       const int s = it & 1;
       FA_TRACE_EV(trc, 10);
       const uint32_t stat = sbase + C::kStat + s * 1024 + w * 256;   // lse2 / D of my 64 query columns
@@ -459,6 +485,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_ld_x32(tS + lane_sel + w * 64 + 32, r1);
         ptx::tmem_wait_ld();
       }
+      FA_TRACE_EV(trc, 30);
       const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
       const int lim = n_abs - shift;                     // causal: visible iff q >= lim
       float cs = c2;
@@ -486,6 +513,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
         p[c + 2] = ptx::ex2(y.x); p[c + 3] = ptx::ex2(y.y);
       }
+      FA_TRACE_EV(trc, 31);
       if (diag || ragged_k) {                            // CTA/warp-uniform: only diagonal and last key tiles
 #pragma unroll
         for (int c = 0; c < 64; ++c)
@@ -503,8 +531,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           }
           pk[c] = pack2(lo, hi, kBF16);
         }
+        FA_TRACE_EV(trc, 32);
         ptx::tmem_st_x32(tS + lane_sel + w * 64, pk);     // P^T half w lives in columns [64w, 64w+32)
         ptx::tmem_wait_st();
+        FA_TRACE_EV(trc, 33);
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(B.p_ready);
@@ -636,7 +666,7 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
   }
 }
 
-template <int D, bool kBF16, bool kDropout, bool kMask>
+template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
 const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
   CUtensorMap tq, tk, tv, tdo;
@@ -666,8 +696,17 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
 
   const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * a.nblk * 32 * sizeof(float);
   if (cudaMemsetAsync(p.dq_accum, 0, acc_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq_accum) failed";
+  // num_splits == 1: turn counters for the ordered dQ accumulation, a stream-ordered temporary (the
+  // ABI has no argument for them; freed on the same stream right after the kernel)
+  a.sem = nullptr;
+  if (kOrdered) {
+    const size_t sem_bytes = (size_t)p.b * p.h * a.nqt * sizeof(int);
+    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sem), sem_bytes, stream) != cudaSuccess)
+      return "cudaMallocAsync(dq turn counters) failed";
+    if (cudaMemsetAsync(a.sem, 0, sem_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq turn counters) failed";
+  }
 
-  auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask>;
+  auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask, kOrdered>;
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kBytes) != cudaSuccess)
@@ -677,6 +716,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   dim3 grid((p.sk + kT - 1) / kT, p.hk, p.b);
   kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, a);
   cudaError_t err = cudaGetLastError();
+  if (a.sem) cudaFreeAsync(a.sem, stream);
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
   dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale, a.d,
@@ -698,10 +738,9 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
-  if (p.mask && p.cu_q) return false;
+  if (p.mask && (p.cu_q || p.deterministic)) return false;   // bias + ordered dQ: all-shapes kernels
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
-  if (p.deterministic) return false;                  // reduce-add order is not fixed
   if (!p.dq_accum) return false;
   // scratch contract (include/flash_attn.h): dq_accum >= b * sq_rounded * h * d_rounded floats
   if (p.sq_rounded % kT || p.sq_rounded < p.sq || p.d_rounded < (p.d + 31) / 32 * 32) return false;
@@ -710,7 +749,10 @@ bool tc_bwd_supported(const Params &p) {
 
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   const bool drop = p.p_dropout > 0.f;
-#define FA_MASKED(DD, BF, DR) (p.mask ? launch_tc_bwd_t<DD, BF, DR, true>(p, stream) : launch_tc_bwd_t<DD, BF, DR, false>(p, stream))
+#define FA_MASKED(DD, BF, DR)                                                              \
+  (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, false>(p, stream)                            \
+          : p.deterministic ? launch_tc_bwd_t<DD, BF, DR, false, true>(p, stream)          \
+                            : launch_tc_bwd_t<DD, BF, DR, false, false>(p, stream))
 #define FA_DISPATCH(DD)                                                                          \
   if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                          \
                              : FA_MASKED(DD, true, false);                        \

@@ -119,3 +119,13 @@ def time_mask(b, s, h, d, iters=10):
 
 if __name__ == "__main__" and WHICH in ("all", "mask"):
     time_mask(8, 4096, 32, 128)
+
+
+if __name__ == "__main__" and WHICH in ("all", "det"):
+    import functools
+    _orig = api.flash_attn_bwd
+    api.flash_attn_bwd = functools.partial(_orig, deterministic=True)
+    print("deterministic dQ (num_splits == 1):")
+    time_bwd(16, 4096, 32, 128, True)
+    time_bwd(16, 4096, 32, 128, False)
+    api.flash_attn_bwd = _orig
