@@ -129,3 +129,38 @@ if __name__ == "__main__" and WHICH in ("all", "det"):
     time_bwd(16, 4096, 32, 128, True)
     time_bwd(16, 4096, 32, 128, False)
     api.flash_attn_bwd = _orig
+
+
+def time_varlen(lens, h, hk, d, causal, iters=10):
+    """BASELINE.json config 4: packed mixed-length batch through flash_attn_varlen_fwd / _bwd."""
+    import itertools
+    cu = torch.tensor([0] + list(itertools.accumulate(lens)), dtype=torch.int32, device="cuda")
+    total, mx = sum(lens), max(lens)
+    q = torch.randn(total, h, d, device="cuda", dtype=torch.bfloat16)
+    k = torch.randn(total, hk, d, device="cuda", dtype=torch.bfloat16); v = torch.randn_like(k)
+    do = torch.randn_like(q)
+    out, lse, _, _ = api.flash_attn_varlen_fwd(q, k, v, cu, cu, mx, mx, is_causal=causal)
+    pf = api.last_path()
+    api.flash_attn_varlen_bwd(do, q, k, v, out, lse, cu, cu, mx, mx, is_causal=causal)
+    pb_ = api.last_path()
+    torch.cuda.synchronize()
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    e[0].record()
+    for _ in range(iters):
+        api.flash_attn_varlen_fwd(q, k, v, cu, cu, mx, mx, is_causal=causal)
+    e[1].record()
+    for _ in range(iters):
+        api.flash_attn_varlen_bwd(do, q, k, v, out, lse, cu, cu, mx, mx, is_causal=causal)
+    e[2].record(); torch.cuda.synchronize()
+    fl = sum(4.0 * h * s * s * d * (0.5 if causal else 1.0) for s in lens)
+    tf, tb = e[0].elapsed_time(e[1]) / iters, e[1].elapsed_time(e[2]) / iters
+    print(f"varlen C4 mix {len(lens)} seqs {total} tokens h{h}/{hk} d{d} causal={causal} paths={pf}/{pb_}: "
+          f"fwd {tf:.3f} ms {fl / tf / 1e9:.1f} TFLOP/s, bwd {tb:.3f} ms {2.5 * fl / tb / 1e9:.1f} TFLOP/s", flush=True)
+
+
+if __name__ == "__main__" and WHICH in ("all", "varlen"):
+    C4 = [128, 8192, 512, 4096, 1000, 2048, 256, 6000]
+    for d_ in (128, 64):
+        for c_ in (True, False):
+            time_varlen(C4, 32, 8, d_, c_)
+    time_varlen([128, 256] * 64, 32, 8, 128, True)      # the short end alone
