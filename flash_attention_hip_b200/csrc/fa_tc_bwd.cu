@@ -330,6 +330,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::mbar_wait(B.ds_ready, it & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 6);
+        // dQ first: it heads the longest dependency chain of the loop (dQ -> drain -> dP^T(it+1) -> dS
+        // -> dQ(it+1), through the shared tensor-memory columns); dK only feeds its own accumulator
+#pragma unroll
+        for (int ks = 0; ks < kT / 16; ++ks)                               // (5) dQ = dS K
+          ptx::mma_ss(tDP, ptx::smem_desc_at(hi_mn, b16, C::kDS + ks * 2048),
+                      ptx::smem_desc_at(hi_mn, b16, C::kK + ks * 2048), id_mn_mn, ks > 0);
+        ptx::mma_commit(B.dq_full);
 #pragma unroll
         for (int ks = 0; ks < kT / 16; ++ks) {                             // (4) dK += dS^T Q
           const uint32_t aoff = (ks / 4) * C::kSub + (ks % 4) * 32;
@@ -337,11 +344,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                       id_k_mn, it > 0 || ks > 0);
         }
         ptx::mma_commit(B.q_empty + 8 * s);
-#pragma unroll
-        for (int ks = 0; ks < kT / 16; ++ks)                               // (5) dQ = dS K
-          ptx::mma_ss(tDP, ptx::smem_desc_at(hi_mn, b16, C::kDS + ks * 2048),
-                      ptx::smem_desc_at(hi_mn, b16, C::kK + ks * 2048), id_mn_mn, ks > 0);
-        ptx::mma_commit(B.dq_full);
       }
       ptx::mma_commit(B.acc_done);
     }
@@ -570,7 +572,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
       FA_TRACE_EV(trc, 15);
-      if (it > 0) ptx::mbar_wait(B.dq_full, (it - 1) & 1);   // GEMMs (4),(5) of it-1 have read dS^T
+      // GEMMs (5),(4) of it-1 have read dS^T: q_empty is committed after the later of the two (dK)
+      if (it > 0) ptx::mbar_wait(B.q_empty + 8 * ((it - 1) & 1), ((it - 1) >> 1) & 1);
       FA_TRACE_EV(trc, 16);
       {
         const uint32_t rowp = sbase + C::kDS + w * C::kSub + n * 128;
