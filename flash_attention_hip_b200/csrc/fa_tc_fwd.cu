@@ -195,7 +195,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 #ifdef FA_TRACE
-  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0;
+  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == gridDim.z / 2;
 #endif
 
   if (warp >= 8) {
@@ -525,6 +525,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       a.lse[((size_t)bidx * a.h + head) * a.sq + row] =
           l_run > 0.f ? (log2f(l_run) + m_use * c2) * kLn2 : INFINITY;
     }
+    FA_TRACE_EV(trs, 16);
   }
 
   // ---- teardown ----------------------------------------------------------------------

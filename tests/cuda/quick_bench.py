@@ -30,6 +30,23 @@ if __name__ == "__main__" and WHICH in ("all", "fwd"):
     time_fwd(4, 8192, 16, 128, False)
     time_fwd(16, 4096, 32, 64, True)
 
+if __name__ == "__main__" and WHICH == "fdrop":
+    for _ in range(2):
+        time_fwd(16, 4096, 32, 128, True, p=0.1)
+        time_fwd(16, 4096, 32, 128, False, p=0.1)
+    time_fwd(8, 2048, 16, 128, True, p=0.1)
+    time_fwd(16, 4096, 32, 64, True, p=0.1)
+
+if __name__ == "__main__" and WHICH == "fscan":   # fixed cost per CTA vs cost per KV tile, dropout forward
+    for sl, bb in ((512, 1024), (1024, 256), (2048, 64), (4096, 16)):
+        time_fwd(bb, sl, 32, 128, False, p=0.1)
+    for sl, bb in ((512, 1024), (1024, 256), (2048, 64), (4096, 16)):
+        time_fwd(bb, sl, 32, 128, False, p=0.0)
+
+if __name__ == "__main__" and WHICH == "fscanc":
+    for sl, bb in ((512, 1024), (1024, 256), (2048, 64), (4096, 16), (8192, 4), (16384, 1)):
+        time_fwd(bb, sl, 32, 128, True, p=0.1)
+
 
 def time_bwd(b, s, h, d, causal, p=0.0, iters=10, dtype=torch.bfloat16, hk=None):
     hk = hk or h

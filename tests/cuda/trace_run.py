@@ -10,7 +10,7 @@ from flash_attention_hip_b200 import api
 which = sys.argv[1] if len(sys.argv) > 1 else "bwd"
 p = float(sys.argv[2]) if len(sys.argv) > 2 else 0.0
 causal = bool(int(sys.argv[3])) if len(sys.argv) > 3 else False
-b, s, h, d = 2, 4096, 16, 128
+b, s, h, d = int(os.environ.get("TRACE_B", 2)), int(os.environ.get("TRACE_S", 4096)), int(os.environ.get("TRACE_H", 16)), 128
 q, k, v, do = (torch.randn(b, s, h, d, device="cuda", dtype=torch.bfloat16) for _ in range(4))
 kw = dict(p_dropout=p, is_causal=causal, seed=1, offset=0)
 out, lse, _, _ = api.flash_attn_fwd(q, k, v, **kw)
@@ -32,6 +32,12 @@ for role in range(8):
     if 254 in wall and 255 in wall and wall[255] > wall[254]:
         print(f"    SM clock during the traced CTA: {(clk[253] - clk[252]) / (wall[255] - wall[254]) * 1e3:.0f} MHz")
     t0 = ev[0][0]
+    if os.environ.get("TRACE_RAW") == "1":
+        base = int(os.environ.get("TRACE_T0", 0)) or t0
+        if not os.environ.get("TRACE_T0"):
+            os.environ["TRACE_T0"] = str(t0)
+        print(f"--- role {role} raw: " + " ".join(f"{e}@{t - base}" for t, e in ev[:int(os.environ.get('TRACE_N', 60))]))
+        continue
     print(f"--- role {role}: {n} events, span {ev[-1][0] - t0} cycles")
     # mean delta between consecutive event ids over the middle half
     lo, hi = n // 4, 3 * n // 4
