@@ -105,7 +105,7 @@ def flash_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, p_dropo
                    softmax_scale: Optional[float] = None, is_causal: bool = False,
                    return_softmax: bool = False, seed: int = 0, offset: int = 0,
                    attn_mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                   stream: Optional[torch.cuda.Stream] = None):
+                   lse: Optional[torch.Tensor] = None, stream: Optional[torch.cuda.Stream] = None):
     """Dense forward.  q [b, sq, h, d]; k, v [b, sk, hk, d]; fp16 or bf16, contiguous.
     Returns (out, softmax_lse [b, h, sq] fp32, softmax or None, rng_state [2] int64)."""
     assert q.is_cuda and q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
@@ -116,7 +116,8 @@ def flash_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, p_dropo
     sq_r, sk_r, d_r = round_up(sq, 128), round_up(sk, 128), round_up(d, 32)
     if out is None:
         out = torch.empty_like(q)
-    lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
+    if lse is None:
+        lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
     sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
     rng = torch.empty(2, dtype=torch.int64, device=q.device)
     mptr, mdims, _keep = _mask_args(attn_mask)
@@ -133,7 +134,7 @@ def flash_attn_varlen_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                           max_seqlen_q: int, max_seqlen_k: int, *, p_dropout: float = 0.0,
                           softmax_scale: Optional[float] = None, is_causal: bool = False,
                           return_softmax: bool = False, seed: int = 0, offset: int = 0,
-                          out: Optional[torch.Tensor] = None,
+                          out: Optional[torch.Tensor] = None, lse: Optional[torch.Tensor] = None,
                           stream: Optional[torch.cuda.Stream] = None):
     """Packed forward.  q [total_q, h, d]; k, v [total_k, hk, d]; cu_seqlens int32 [b+1] on device.
     Returns (out, softmax_lse [b, h, max_seqlen_q], softmax or None, rng_state)."""
@@ -146,7 +147,8 @@ def flash_attn_varlen_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
     sq_r, sk_r, d_r = round_up(max_seqlen_q, 128), round_up(max_seqlen_k, 128), round_up(d, 32)
     if out is None:
         out = torch.empty_like(q)
-    lse = torch.full((b, h, max_seqlen_q), float("inf"), dtype=torch.float32, device=q.device)
+    if lse is None:
+        lse = torch.full((b, h, max_seqlen_q), float("inf"), dtype=torch.float32, device=q.device)
     sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
     rng = torch.empty(2, dtype=torch.int64, device=q.device)
     ok = lib().flash_attn_varlen_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k),
@@ -194,7 +196,8 @@ def flash_attn_bwd(dout, q, k, v, out, softmax_lse, *, p_dropout: float = 0.0,
 def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seqlens_k,
                           max_seqlen_q: int, max_seqlen_k: int, *, p_dropout: float = 0.0,
                           softmax_scale: Optional[float] = None, is_causal: bool = False,
-                          deterministic: bool = False, seed: int = 0, offset: int = 0,
+                          deterministic: bool = False, seed: int = 0, offset: int = 0, scratch=None,
+                          grads: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
                           stream: Optional[torch.cuda.Stream] = None):
     """Packed backward; returns (dq, dk, dv)."""
     for t in (dout, q, k, v, out):
@@ -204,8 +207,8 @@ def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seql
     b = cu_seqlens_q.numel() - 1
     scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
     sq_r, sk_r, d_r = round_up(max_seqlen_q, 128), round_up(max_seqlen_k, 128), round_up(d, 32)
-    softmax_d, dq_accum = _bwd_scratch(b, sq_r, h, d_r, q.device)
-    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    softmax_d, dq_accum = scratch if scratch is not None else _bwd_scratch(b, sq_r, h, d_r, q.device)
+    dq, dk, dv = grads if grads is not None else (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
     ok = lib().flash_attn_varlen_bwd(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
                                      _ptr(softmax_lse), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), None,
                                      _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum), b, max_seqlen_q,
