@@ -79,6 +79,14 @@ if __name__ == "__main__" and WHICH in ("all", "bwd"):
     time_bwd(16, 4096, 32, 64, True)
     time_bwd(4, 8192, 32, 128, True, hk=8)
 
+if __name__ == "__main__" and WHICH == "bdrop":
+    for _ in range(2):
+        time_bwd(16, 4096, 32, 128, True, p=0.1)
+        time_bwd(16, 4096, 32, 128, False, p=0.1)
+    time_bwd(8, 2048, 16, 128, True, p=0.1)
+    time_bwd(16, 4096, 32, 64, True, p=0.1)
+    time_bwd(4, 8192, 32, 128, True, p=0.1, hk=8)
+
 
 def time_membound(b, sq, sk, h, d, causal=False, iters=50, hk=None):
     """Short-sequence / decode-like shapes are HBM- or latency-bound: report achieved GB/s on the
