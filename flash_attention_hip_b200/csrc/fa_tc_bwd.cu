@@ -214,7 +214,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 384;
 
 #ifdef FA_TRACE
-  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == 0;
+  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == gridDim.z / 2;
 #endif
   if (warp >= 8 && warp < 12) {
     // =========================== producer warpgroup ======================================
@@ -590,15 +590,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
     ptx::mbar_wait(B.acc_done, 0);
     ptx::tc_fence_after();
+    // Each thread owns half a ROW of dK / dV; writing it out directly costs one 16-byte store per lane and
+    // row (32 rows, 32 cache lines per instruction: ~8600 cycles per CTA, traced).  Stage both tiles in the
+    // idle Q ring instead (16-byte chunks XOR-swizzled by row) and let all 256 threads write whole rows.
     constexpr int kHalf = D / 2;                         // columns per warp half
-    const size_t tok = ktok0 + n_abs;
-    uint16_t *dkp = static_cast<uint16_t *>(a.dk) + (tok * a.hk + hk) * a.d + w * kHalf;
-    uint16_t *dvp = static_cast<uint16_t *>(a.dv) + (tok * a.hk + hk) * a.d + w * kHalf;
+    constexpr int kRowChunks = D / 8;                    // 16-byte chunks per row
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
       const uint32_t tsrc = (which ? tDK : tDV) + lane_sel + w * kHalf;
       const float mul = n_it == 0 ? 0.f : (which ? a.scale : a.rp_dropout);
-      uint4 *dst = reinterpret_cast<uint4 *>(which ? dkp : dvp);
+      const uint32_t rowp = sbase + C::kQ + which * C::kTile + n * (D * 2);
 #pragma unroll
       for (int c = 0; c < kHalf / 32; ++c) {
         uint32_t v[32];
@@ -609,19 +610,34 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
           for (int x = 0; x < 32; ++x) v[x] = 0;
         }
-        if (kv_valid) {
 #pragma unroll
-          for (int x = 0; x < 4; ++x) {
-            uint4 o;
-            o.x = pack2(__uint_as_float(v[8 * x]) * mul, __uint_as_float(v[8 * x + 1]) * mul, kBF16);
-            o.y = pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16);
-            o.z = pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16);
-            o.w = pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16);
-            if (w * kHalf + c * 32 + x * 8 < a.d) dst[c * 4 + x] = o;
-          }
+        for (int x = 0; x < 4; ++x) {
+          const int chunk = (w * kHalf + c * 32) / 8 + x;
+          st_shared_v4(rowp + ((chunk ^ (n & 7)) << 4),
+                       pack2(__uint_as_float(v[8 * x]) * mul, __uint_as_float(v[8 * x + 1]) * mul, kBF16),
+                       pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16),
+                       pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16),
+                       pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16));
         }
       }
     }
+    ptx::named_bar_sync(2, 256);                         // the eight compute warps
+    const int rows_valid = min(kT, sk - j * kT);
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      uint16_t *gbase = static_cast<uint16_t *>(which ? a.dk : a.dv) + ((ktok0 + (size_t)j * kT) * a.hk + hk) * a.d;
+      const uint32_t tile = sbase + C::kQ + which * C::kTile;
+#pragma unroll
+      for (int idx = threadIdx.x; idx < kT * kRowChunks; idx += 256) {
+        const int r = idx / kRowChunks, ch = idx % kRowChunks;
+        uint4 o;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
+                     : "r"(tile + r * (D * 2) + ((ch ^ (r & 7)) << 4)));
+        if (r < rows_valid && ch * 8 < a.d)
+          *reinterpret_cast<uint4 *>(gbase + (size_t)r * a.hk * a.d + ch * 8) = o;
+      }
+    }
+    FA_TRACE_EV(trc, 18);
   }
 
   // ---- teardown -------------------------------------------------------------------------------
