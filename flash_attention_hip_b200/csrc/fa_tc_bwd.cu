@@ -590,6 +590,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
     ptx::mbar_wait(B.acc_done, 0);
     ptx::tc_fence_after();
+    FA_TRACE_EV(trc, 19);
     // Each thread owns half a ROW of dK / dV; writing it out directly costs one 16-byte store per lane and
     // row (32 rows, 32 cache lines per instruction: ~8600 cycles per CTA, traced).  Stage both tiles in the
     // idle Q ring instead (16-byte chunks XOR-swizzled by row) and let all 256 threads write whole rows.
@@ -621,7 +622,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
     }
+    FA_TRACE_EV(trc, 34);
     ptx::named_bar_sync(2, 256);                         // the eight compute warps
+    FA_TRACE_EV(trc, 35);
     const int rows_valid = min(kT, sk - j * kT);
 #pragma unroll
     for (int which = 0; which < 2; ++which) {

@@ -1,5 +1,6 @@
 #!/bin/bash
-# One GPU-box pass: parity tests, quick timings, contract bench, ncu launch list + full captures.
+# One GPU-box pass: parity tests, quick timings, contract bench (+ reference arm), ncu launch list.
+# The `ncu --set full` capture is a separate call (tests/cuda/gpu_ncu_full.sh).
 set -u
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
@@ -10,7 +11,4 @@ python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/bench_ref.log
 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu > gpurun_out/ncu_bench.log 2>&1
-python tests/cuda/prof_case.py 16 2 > gpurun_out/plain_prof.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'tc_fwd_kernel|tc_bwd_kernel|dq_convert|preprocess' -s 4 -c 4 \
-    -f -o gpurun_out/prof_fwd_bwd python tests/cuda/prof_case.py 16 2 > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/ncu_full.log
+tail -2 gpurun_out/ncu_bench.log
