@@ -48,11 +48,15 @@ constexpr float kLn2 = 0.6931471805599453f;
 
 template <int D>
 struct Cfg {
-  static constexpr int kStages = D == 128 ? 2 : 4;            // K and V ring depth
+  // D = 256 (head sizes 136..256): one 128-row query tile per CTA -- O alone takes 256 of the 512 tensor-
+  // memory columns -- and single K / V buffers (Q + K + V = 192 KB), so the tensor pipe waits for the
+  // softmax: roughly half the rate of the two-tile kernels, two orders above the all-shapes family.
+  static constexpr int kStages = D == 128 ? 2 : D == 64 ? 4 : 1;   // K and V ring depth
+  static constexpr int kQTiles = D == 256 ? 1 : 2;            // query tiles (softmax warpgroups at work) per CTA
   static constexpr uint32_t kTileBytes = kTileM * D * 2;      // one Q/K/V tile
   static constexpr uint32_t kSubBytes = kTileM * 128;         // one [128 x 64] swizzled sub-tile
   static constexpr uint32_t kSmemQ = 0;
-  static constexpr uint32_t kSmemK = 2 * kTileBytes;
+  static constexpr uint32_t kSmemK = kQTiles * kTileBytes;
   static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
   static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
   static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8;
@@ -132,7 +136,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     sq = a.cu_q[bidx + 1] - q0; sk = a.cu_k[bidx + 1] - k0;
     bcoord = 0;
   }
-  const int m0 = qblk * 2 * kTileM;
+  const int m0 = qblk * C::kQTiles * kTileM;
   if (m0 >= sq) return;                       // whole CTA leaves before any barrier
   const int hk = head / (a.h / a.hk);
   const int shift = sk - sq;                  // causal: key j visible to row i iff j <= i + shift
@@ -141,7 +145,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     const int r0 = m0 + t * kTileM;
-    int n = r0 < sq ? nkv : 0;
+    int n = (r0 < sq && t < C::kQTiles) ? nkv : 0;
     if (a.causal && n) {
       const int last = min(r0 + kTileM, sq) - 1 + shift;   // last visible key of the tile
       n = last < 0 ? 0 : min(nkv, last / kTileN + 1);
@@ -149,7 +153,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ntile[t] = n;
   }
   const int nmax = max(ntile[0], ntile[1]);
-  const bool has_tile1 = m0 + kTileM < sq;
+  const bool has_tile1 = C::kQTiles == 2 && m0 + kTileM < sq;
 
   // ---- barriers, tensor memory ----------------------------------------------
   const uint32_t bar0 = sbase + C::kSmemBar;
@@ -320,6 +324,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (j + 1 < nmax) ptx::mma_commit(B.k_empty + 8 * sn);
       }
     }
+  } else if ((warp >> 2) >= C::kQTiles) {
+    ptx::setmaxnreg_dec<40>();                        // D = 256: the second softmax warpgroup has no tile
   } else {
     // ======================= softmax warpgroups ===================================
     ptx::setmaxnreg_inc<232>();
@@ -551,7 +557,7 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 }
 
 bool tc_fwd_supported(const Params &p) {
-  if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
+  if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
   if (p.softmax_ret) return false;               // S_dmask output: all-shapes kernel
   if (p.mask && p.cu_q) return false;
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
@@ -595,7 +601,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
       return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
     attr_set = true;
   }
-  dim3 grid((p.sq + 2 * kTileM - 1) / (2 * kTileM), p.h, p.b);
+  dim3 grid((p.sq + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM), p.h, p.b);
   kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tq, tk, tv, a);
   const cudaError_t err = cudaGetLastError();
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
@@ -610,6 +616,7 @@ const char *launch_tc_fwd(const Params &p, cudaStream_t stream) {
   if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                        \
                              : FA_MASKED(DD, true, false);                      \
   return drop ? FA_MASKED(DD, false, true) : FA_MASKED(DD, false, false);
+  if (p.d > 128) { FA_DISPATCH(256) }
   if (p.d > 64) { FA_DISPATCH(128) }
   FA_DISPATCH(64)
 #undef FA_DISPATCH

@@ -87,6 +87,11 @@ if __name__ == "__main__" and WHICH == "bdrop":
     time_bwd(16, 4096, 32, 64, True, p=0.1)
     time_bwd(4, 8192, 32, 128, True, p=0.1, hk=8)
 
+if __name__ == "__main__" and WHICH == "bigd":
+    for d in (160, 192, 256):
+        time_fwd(4, 2048, 16, d, True)
+        time_bwd(4, 2048, 16, d, True)
+
 
 def time_membound(b, sq, sk, h, d, causal=False, iters=50, hk=None):
     """Short-sequence / decode-like shapes are HBM- or latency-bound: report achieved GB/s on the

@@ -38,6 +38,15 @@ CASES = {
     "d32_fp16": lambda: cases.dense(1, 128, 384, 2, 2, 32, is_bf16=False),
     "d104_dropout": lambda: cases.dense(1, 384, 384, 2, 1, 104, p_dropout=0.1, seed=5, offset=0),
     "d8_tiny": lambda: cases.dense(1, 130, 130, 1, 1, 8, is_causal=True),
+    # head sizes 136..256 ride the one-tile D = 256 kernel
+    "d256_causal": lambda: cases.dense(2, 384, 384, 2, 2, 256, is_causal=True),
+    "d256_ragged_gqa": lambda: cases.dense(1, 300, 450, 4, 2, 256),
+    "d192_dropout": lambda: cases.dense(1, 257, 257, 2, 2, 192, is_causal=True, p_dropout=0.1, seed=3, offset=9),
+    "d160_fp16": lambda: cases.dense(1, 200, 333, 2, 1, 160, is_bf16=False),
+    "d136_sq_gt_sk_causal": lambda: cases.dense(1, 450, 300, 2, 2, 136, is_causal=True),
+    "d224_tiny_5x700": lambda: cases.dense(1, 5, 700, 2, 1, 224, is_causal=True),
+    "d256_packed": lambda: cases.varlen([200, 77, 300], [200, 77, 300], 4, 2, 256, is_causal=True),
+    "d200_packed_sq_ne_sk": lambda: cases.varlen([100, 300], [260, 128], 2, 2, 200),
     "c2_small_b2h4s2048d128": lambda: cases.dense(2, 2048, 2048, 4, 4, 128, is_causal=True),
 }
 
