@@ -88,6 +88,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 const char *launch_generic_fwd(const Params &p, cudaStream_t stream);
 const char *launch_generic_bwd(const Params &p, cudaStream_t stream);
 const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream);
+// all-shapes backward on warp-level MMAs (fa_mma_bwd.cu); what launch_generic_bwd runs
+const char *launch_mma_bwd(const Params &p, cudaStream_t stream);
 
 // tcgen05 paths; return nullptr on success, else a static error string.
 bool tc_fwd_supported(const Params &p);

@@ -307,7 +307,11 @@ const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream) {
 
 const char *launch_generic_bwd(const Params &p, cudaStream_t stream) {
   if (p.d > kMaxD || p.d % 8) return "generic backward: head_size must be a multiple of 8 and <= 256";
+#ifdef FA_SCALAR_BWD
   return p.is_bf16 ? launch_bwd_t<__nv_bfloat16>(p, stream) : launch_bwd_t<__half>(p, stream);
+#else
+  return launch_mma_bwd(p, stream);
+#endif
 }
 
 }  // namespace fa

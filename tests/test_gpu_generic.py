@@ -20,6 +20,12 @@ CASES = {
     "d256": lambda: cases.dense(1, 40, 72, 2, 2, 256),
     "varlen": lambda: cases.varlen([5, 64, 1, 33], [7, 64, 9, 33], 4, 2, 64, is_causal=True, p_dropout=0.2, seed=3, offset=2**33 + 1),
     "varlen_empty_seq": lambda: cases.varlen([16, 0, 20], [16, 8, 0], 2, 2, 16),
+    # the backward of head sizes above 128 always comes here (fa_mma_bwd.cu)
+    "d256_causal_gqa_drop": lambda: cases.dense(2, 200, 200, 4, 2, 256, is_causal=True, p_dropout=0.1, seed=8, offset=3),
+    "d192_ragged": lambda: cases.dense(1, 130, 333, 2, 2, 192),
+    "d160_sq_gt_sk_causal_fp16": lambda: cases.dense(1, 300, 150, 2, 1, 160, is_causal=True, is_bf16=False),
+    "d136_varlen": lambda: cases.varlen([100, 1, 77], [130, 64, 77], 2, 2, 136, is_causal=True),
+    "d96_multi_tile": lambda: cases.dense(1, 257, 257, 2, 2, 96, is_causal=True, p_dropout=0.3, seed=1, offset=1),
 }
 
 
