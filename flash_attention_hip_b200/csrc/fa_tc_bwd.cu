@@ -152,7 +152,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t sbase = ptx::smem_u32(smem_raw);
   if (sbase & 1023u) __trap();   // the swizzled tiles need a 1024-byte aligned base
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: the role branches are then provably warp-uniform, and tcgen05.mma under
+  // elect.sync is issued without a per-instruction election loop (see fa_tc_fwd.cu)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   // ---- problem coordinates ---------------------------------------------------------
   const int j = blockIdx.x, hk = blockIdx.y, bidx = blockIdx.z;
@@ -273,7 +275,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, mdo, B.do_full, c * 64, hq, qrow0 + i * kT, bcoord);
         }
       }
-    } else if (warp == kMmaWarp && lane == 0) {
+    } else if (warp == kMmaWarp && ptx::elect_one()) {
       // ---- MMA issuer -----------------------------------------------------------------------
       constexpr uint32_t fmt = kBF16 ? ptx::kFmtBF16 : ptx::kFmtF16;
       constexpr uint32_t id_kk = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorK, kT, kT);     // (1) (2)

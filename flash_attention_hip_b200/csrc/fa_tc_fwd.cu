@@ -59,10 +59,10 @@ struct Cfg {
   static constexpr uint32_t kSmemK = kQTiles * kTileBytes;
   static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
   static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
-  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8;
-  static constexpr uint32_t kSmemDesc = kSmemBar + 256;       // 3 x 128 B tensor-map staging (packed inputs)
+  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8 + 7;
+  static constexpr uint32_t kSmemDesc = kSmemBar + 512;       // 3 x 128 B tensor-map staging (packed inputs)
   static constexpr uint32_t kSmemBytes = kSmemDesc + 3 * 128 + 1024;  // + alignment slack
-  static_assert(kNumBars * 8 + 16 <= 256, "barrier block overflows");
+  static_assert(kNumBars * 8 + 16 <= 512, "barrier block (+ tmem slot, item queue) overflows");
   static_assert(kSmemBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
 
@@ -71,6 +71,7 @@ __device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][3];
 
 struct Bars {
   uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_lo, p_hi, pv_done;  // first of each group
+  uint32_t q_empty, o_free /*[2]*/, sched_full /*[2]*/, sched_empty /*[2]*/;
 };
 
 __device__ __forceinline__ uint32_t pack_pair(float lo, float hi, bool bf16) {
@@ -115,6 +116,16 @@ struct TcFwdArgs {
   uint32_t drop_threshold;
   uint32_t key0, key1, ctr3;   // Philox key / counter word 3 (csrc/philox_spec.h)
   int causal;
+  int nqb, n_items;      // query blocks per (batch, head); work items = nqb * h * b
+  int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
+  int *sched;            // global item counter (stream-ordered temporary, zeroed before the launch)
+};
+
+// One unit of work: 256 (128 when D = 256) query rows of one (batch, head).
+struct Item {
+  int bidx, head, hk, q0, k0, sq, sk, bcoord, m0, shift, nkv, nmax;
+  int ntile[2];
+  bool has_tile1, valid;
 };
 
 template <int D, bool kBF16, bool kDropout, bool kMask>
@@ -125,35 +136,46 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *sgen = smem_raw + (sbase - ptx::smem_u32(smem_raw));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: the compiler then knows the role branches are warp-uniform, and with
+  // elect.sync inside them it issues TMA / tcgen05.mma without a per-instruction election loop
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
-  // ---- problem coordinates -------------------------------------------------
-  const int bidx = blockIdx.z, head = blockIdx.y;
-  const int qblk = a.causal ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;  // heavy first
-  int q0 = 0, k0 = 0, sq = a.sq, sk = a.sk, bcoord = bidx;
-  if (a.cu_q) {
-    q0 = a.cu_q[bidx]; k0 = a.cu_k[bidx];
-    sq = a.cu_q[bidx + 1] - q0; sk = a.cu_k[bidx + 1] - k0;
-    bcoord = 0;
-  }
-  const int m0 = qblk * C::kQTiles * kTileM;
-  if (m0 >= sq) return;                       // whole CTA leaves before any barrier
-  const int hk = head / (a.h / a.hk);
-  const int shift = sk - sq;                  // causal: key j visible to row i iff j <= i + shift
-  const int nkv = (sk + kTileN - 1) / kTileN;
-  int ntile[2];
-#pragma unroll
-  for (int t = 0; t < 2; ++t) {
-    const int r0 = m0 + t * kTileM;
-    int n = (r0 < sq && t < C::kQTiles) ? nkv : 0;
-    if (a.causal && n) {
-      const int last = min(r0 + kTileM, sq) - 1 + shift;   // last visible key of the tile
-      n = last < 0 ? 0 : min(nkv, last / kTileN + 1);
+  // ---- work items ------------------------------------------------------------
+  // Linear order: query blocks fastest inside a (batch, head), heaviest (last) causal block first, so
+  // the CTAs running at any moment share a handful of heads' K/V in L2.  Dense inputs: one CTA per SM
+  // takes items from a global counter (a.sched) until they run out, and its TMA and MMA warps run
+  // ahead into the next item while the softmax warps finish the current one.  Packed inputs: one
+  // item per CTA (the tensor maps are bounded to ONE sequence per CTA, see patch_rows).
+  auto decode = [&](int L) {
+    Item it;
+    const int hb = L / a.nqb, r = L % a.nqb;
+    it.head = hb % a.h; it.bidx = hb / a.h;
+    const int qblk = a.causal ? a.nqb - 1 - r : r;
+    it.q0 = 0; it.k0 = 0; it.sq = a.sq; it.sk = a.sk; it.bcoord = it.bidx;
+    if (a.cu_q) {
+      it.q0 = a.cu_q[it.bidx]; it.k0 = a.cu_k[it.bidx];
+      it.sq = a.cu_q[it.bidx + 1] - it.q0; it.sk = a.cu_k[it.bidx + 1] - it.k0;
+      it.bcoord = 0;
     }
-    ntile[t] = n;
-  }
-  const int nmax = max(ntile[0], ntile[1]);
-  const bool has_tile1 = C::kQTiles == 2 && m0 + kTileM < sq;
+    it.m0 = qblk * C::kQTiles * kTileM;
+    it.valid = it.m0 < it.sq;
+    it.hk = it.head / (a.h / a.hk);
+    it.shift = it.sk - it.sq;                 // causal: key j visible to row i iff j <= i + shift
+    it.nkv = (it.sk + kTileN - 1) / kTileN;
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      const int r0 = it.m0 + t * kTileM;
+      int n = (r0 < it.sq && t < C::kQTiles) ? it.nkv : 0;
+      if (a.causal && n) {
+        const int last = min(r0 + kTileM, it.sq) - 1 + it.shift;   // last visible key of the tile
+        n = last < 0 ? 0 : min(it.nkv, last / kTileN + 1);
+      }
+      it.ntile[t] = n;
+    }
+    it.nmax = max(it.ntile[0], it.ntile[1]);
+    it.has_tile1 = C::kQTiles == 2 && it.m0 + kTileM < it.sq;
+    return it;
+  };
 
   // ---- barriers, tensor memory ----------------------------------------------
   const uint32_t bar0 = sbase + C::kSmemBar;
@@ -167,10 +189,17 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   B.p_lo = B.s_full + 16;
   B.p_hi = B.p_lo + 16;
   B.pv_done = B.p_hi + 16;
+  B.q_empty = B.pv_done + 16;
+  B.o_free = B.q_empty + 8;
+  B.sched_full = B.o_free + 16;
+  B.sched_empty = B.sched_full + 16;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + C::kSmemBar + C::kNumBars * 8);
+  volatile int *sched_item = reinterpret_cast<volatile int *>(tmem_slot + 2);   // [2]
+  constexpr int kSoftmaxThreads = C::kQTiles * kTileM;
 
   if (threadIdx.x == 0) {
     ptx::mbar_init(B.q_full, 1);
+    ptx::mbar_init(B.q_empty, 1);
     for (int s = 0; s < C::kStages; ++s) {
       ptx::mbar_init(B.k_full + 8 * s, 1);
       ptx::mbar_init(B.k_empty + 8 * s, 1);
@@ -182,6 +211,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::mbar_init(B.p_lo + 8 * t, kTileM);
       ptx::mbar_init(B.p_hi + 8 * t, kTileM);
       ptx::mbar_init(B.pv_done + 8 * t, 1);
+      ptx::mbar_init(B.o_free + 8 * t, kTileM);
+      ptx::mbar_init(B.sched_full + 8 * t, 1);
+      ptx::mbar_init(B.sched_empty + 8 * t, 1 + kSoftmaxThreads);   // MMA lane + every softmax thread
     }
     ptx::fence_mbar_init();
   }
@@ -199,8 +231,16 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 #ifdef FA_TRACE
-  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == gridDim.z / 2;
+  const bool tr_cta = blockIdx.x == gridDim.x / 2;
 #endif
+  // Consumers of the item queue (MMA lane, softmax threads): item number n of this CTA, or -1 at the end.
+  auto next_item = [&](int n) {
+    const int slot = n & 1;
+    ptx::mbar_wait(B.sched_full + 8 * slot, (n >> 1) & 1);
+    const int L = sched_item[slot];
+    ptx::mbar_arrive(B.sched_empty + 8 * slot);
+    return L;
+  };
 
   if (warp >= 8) {
     // ======================= producer warpgroup ================================
@@ -208,38 +248,54 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v;
     if (warp == kLoadWarp && a.cu_q) {
       // packed inputs: rows past this sequence's end must read as zero, not as the next sequence
+      const Item it = decode((int)blockIdx.x);
       const uint32_t sm = ptx::smid();
       if (sm >= (uint32_t)ptx::kMaxSm) __trap();
       const uint32_t d0 = sbase + C::kSmemDesc;
       uint8_t *g0 = sgen + C::kSmemDesc;
-      mq = ptx::patch_rows(tmap_q, &g_fwd_slots[sm][0], d0, g0, (uint32_t)(q0 + sq), lane);
-      mk = ptx::patch_rows(tmap_k, &g_fwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(k0 + sk), lane);
-      mv = ptx::patch_rows(tmap_v, &g_fwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(k0 + sk), lane);
+      mq = ptx::patch_rows(tmap_q, &g_fwd_slots[sm][0], d0, g0, (uint32_t)(it.q0 + it.sq), lane);
+      mk = ptx::patch_rows(tmap_k, &g_fwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(it.k0 + it.sk), lane);
+      mv = ptx::patch_rows(tmap_v, &g_fwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(it.k0 + it.sk), lane);
     }
-    if (warp == kLoadWarp && lane == 0) {
-      // ---- TMA producer --------------------------------------------------------
-      const int qrow = q0 * (a.cu_q ? 1 : 0) + m0;   // packed: absolute token row; dense: row in sequence
-      const int krow = k0 * (a.cu_q ? 1 : 0);
-      ptx::mbar_arrive_expect_tx(B.q_full, (has_tile1 ? 2 : 1) * C::kTileBytes);
-      for (int t = 0; t < (has_tile1 ? 2 : 1); ++t)
-        for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, mq, B.q_full,
-                           c * 64, head, qrow + t * kTileM, bcoord);
-      for (int j = 0; j < nmax; ++j) {
-        const int s = j % C::kStages;
-        const uint32_t ph = (j / C::kStages) & 1;
-        if (j >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
-        ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
-        for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, mk,
-                           B.k_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
-        if (j >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
-        ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
-        for (int c = 0; c < D / 64; ++c)
-          ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, mv,
-                           B.v_full + 8 * s, c * 64, hk, krow + j * kTileN, bcoord);
+    if (warp == kLoadWarp && ptx::elect_one()) {
+      // ---- scheduler + TMA producer ----------------------------------------------
+      int nq = 0;        // items that loaded Q so far (q_full / q_empty phases)
+      int g = 0;         // KV tiles loaded so far (ring stage and phase)
+      for (int n = 0;; ++n) {
+        const int slot = n & 1;
+        if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
+        int L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
+        if (L >= a.n_items) L = -1;
+        sched_item[slot] = L;
+        ptx::mbar_arrive(B.sched_full + 8 * slot);
+        if (L < 0) break;
+        const Item it = decode(L);
+        if (!it.valid || it.nmax == 0) continue;
+        const int qrow = it.q0 * (a.cu_q ? 1 : 0) + it.m0;   // packed: absolute token row; dense: row in sequence
+        const int krow = it.k0 * (a.cu_q ? 1 : 0);
+        if (nq >= 1) ptx::mbar_wait(B.q_empty, (nq - 1) & 1);  // the previous item's S = Q K^T are all done
+        ++nq;
+        ptx::mbar_arrive_expect_tx(B.q_full, (it.has_tile1 ? 2 : 1) * C::kTileBytes);
+        for (int t = 0; t < (it.has_tile1 ? 2 : 1); ++t)
+          for (int c = 0; c < D / 64; ++c)
+            ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, mq, B.q_full,
+                             c * 64, it.head, qrow + t * kTileM, it.bcoord);
+        for (int j = 0; j < it.nmax; ++j, ++g) {
+          const int s = g % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1;
+          if (g >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
+          ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
+          for (int c = 0; c < D / 64; ++c)
+            ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, mk,
+                             B.k_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
+          if (g >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
+          ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
+          for (int c = 0; c < D / 64; ++c)
+            ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, mv,
+                             B.v_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
+        }
       }
-    } else if (warp == kMmaWarp && lane == 0) {
+    } else if (warp == kMmaWarp && ptx::elect_one()) {
       // ---- MMA issuer ------------------------------------------------------------
       constexpr uint32_t fmt = kBF16 ? ptx::kFmtBF16 : ptx::kFmtF16;
       constexpr uint32_t idesc_qk = ptx::make_idesc(fmt, ptx::kMajorK, ptx::kMajorK, kTileM, kTileN);
@@ -272,56 +328,62 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       };
       FA_TRACE_DECL(tr, 0, tr_cta);
-      FA_TRACE_EV(tr, 1);
-      ptx::mbar_wait(B.q_full, 0);
-      ptx::tc_fence_after();
-      if (nmax > 0) {
-        ptx::mbar_wait(B.k_full, 0);
+      int nq = 0, g = 0;             // as in the TMA lane
+      int cnt[2] = {0, 0};           // S tiles issued so far per query tile (s_full / p / pv_done phases)
+      int used[2] = {0, 0};          // items that used O_t so far (o_free phases)
+      for (int n = 0;; ++n) {
+        const int L = next_item(n);
+        if (L < 0) break;
+        const Item it = decode(L);
+        if (!it.valid || it.nmax == 0) continue;
+        const int nt0 = it.ntile[0], nt1 = it.ntile[1], nmax = it.nmax;
+        FA_TRACE_EV(tr, 1);
+        ptx::mbar_wait(B.q_full, nq & 1);
+        ++nq;
+        ptx::tc_fence_after();
+        ptx::mbar_wait(B.k_full + 8 * (g % C::kStages), (g / C::kStages) & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 20);
-        if (ntile[0] > 0) { qk(0, 0); ptx::mma_commit(B.s_full); }
-        if (ntile[1] > 0) { qk(1, 0); ptx::mma_commit(B.s_full + 8); }
-        ptx::mma_commit(B.k_empty);
-#ifdef FA_TRACE
-        FA_TRACE_EV(tr, 21);                 // 20->21: issue of 16 SS MMAs on an idle pipe
-        ptx::mbar_wait(B.s_full + 8, 0);
-        FA_TRACE_EV(tr, 22);                 // 20->22: their execution
-#endif
-      }
-      for (int j = 0; j < nmax; ++j) {
-        const int s = j % C::kStages, sn = (j + 1) % C::kStages;
-        const uint32_t ph = (j / C::kStages) & 1, phn = ((j + 1) / C::kStages) & 1;
         b16 = ptx::opaque(sbase >> 4);
-        FA_TRACE_EV(tr, 2);
-        ptx::mbar_wait(B.v_full + 8 * s, ph);
-        FA_TRACE_EV(tr, 3);
-        if (j < ntile[0]) {
-          FA_TRACE_EV(tr, 4);
-          pv(0, s, j > 0, j & 1);
-          ptx::mma_commit(B.pv_done);
-#ifdef FA_TRACE
-          if (j == 1) {
-            FA_TRACE_EV(tr, 24);             // 4->24: wait P + issue 8 TS MMAs
-            ptx::mbar_wait(B.pv_done, 1);
-            FA_TRACE_EV(tr, 25);             // 24->25: drain
+        if (nt0 > 0) { qk(0, g % C::kStages); ptx::mma_commit(B.s_full); }
+        if (nt1 > 0) { qk(1, g % C::kStages); ptx::mma_commit(B.s_full + 8); }
+        ptx::mma_commit(B.k_empty + 8 * (g % C::kStages));
+        if (nmax == 1) ptx::mma_commit(B.q_empty);           // no further S = Q K^T in this item
+        FA_TRACE_EV(tr, 21);
+        for (int j = 0; j < nmax; ++j, ++g) {
+          const int s = g % C::kStages, sn = (g + 1) % C::kStages;
+          const uint32_t ph = (g / C::kStages) & 1, phn = ((g + 1) / C::kStages) & 1;
+          b16 = ptx::opaque(sbase >> 4);
+          FA_TRACE_EV(tr, 2);
+          ptx::mbar_wait(B.v_full + 8 * s, ph);
+          FA_TRACE_EV(tr, 3);
+          if (j < nt0) {
+            FA_TRACE_EV(tr, 4);
+            // the first P V of an item overwrites O_0: the previous item's epilogue must have read it
+            if (j == 0 && used[0] >= 1) { ptx::mbar_wait(B.o_free, (used[0] - 1) & 1); ptx::tc_fence_after(); }
+            pv(0, s, j > 0, (cnt[0] + j) & 1);
+            ptx::mma_commit(B.pv_done);
           }
-#endif
+          if (j + 1 < nmax) {
+            ptx::mbar_wait(B.k_full + 8 * sn, phn);
+            ptx::tc_fence_after();
+          }
+          FA_TRACE_EV(tr, 5);
+          if (j + 1 < nt0) { qk(0, sn); ptx::mma_commit(B.s_full); }
+          FA_TRACE_EV(tr, 6);
+          if (j < nt1) {
+            FA_TRACE_EV(tr, 7);
+            if (j == 0 && used[1] >= 1) { ptx::mbar_wait(B.o_free + 8, (used[1] - 1) & 1); ptx::tc_fence_after(); }
+            pv(1, s, j > 0, (cnt[1] + j) & 1);
+            ptx::mma_commit(B.pv_done + 8);
+          }
+          ptx::mma_commit(B.v_empty + 8 * s);
+          if (j + 1 < nt1) { qk(1, sn); ptx::mma_commit(B.s_full + 8); }
+          if (j + 1 < nmax) ptx::mma_commit(B.k_empty + 8 * sn);
+          if (j + 2 == nmax) ptx::mma_commit(B.q_empty);     // that was the item's last S = Q K^T
         }
-        if (j + 1 < nmax) {
-          ptx::mbar_wait(B.k_full + 8 * sn, phn);
-          ptx::tc_fence_after();
-        }
-        FA_TRACE_EV(tr, 5);
-        if (j + 1 < ntile[0]) { qk(0, sn); ptx::mma_commit(B.s_full); }
-        FA_TRACE_EV(tr, 6);
-        if (j < ntile[1]) {
-          FA_TRACE_EV(tr, 7);
-          pv(1, s, j > 0, j & 1);
-          ptx::mma_commit(B.pv_done + 8);
-        }
-        ptx::mma_commit(B.v_empty + 8 * s);
-        if (j + 1 < ntile[1]) { qk(1, sn); ptx::mma_commit(B.s_full + 8); }
-        if (j + 1 < nmax) ptx::mma_commit(B.k_empty + 8 * sn);
+        cnt[0] += nt0; cnt[1] += nt1;
+        used[0] += nt0 > 0; used[1] += nt1 > 0;
       }
     }
   } else if ((warp >> 2) >= C::kQTiles) {
@@ -331,15 +393,28 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::setmaxnreg_inc<232>();
     const int t = warp >> 2;                          // query tile of this warpgroup
     const int r_in_tile = (warp & 3) * 32 + lane;     // TMEM lane == row inside the tile
-    const int row = m0 + t * kTileM + r_in_tile;      // row inside the sequence
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem + t * 128 + lane_sel;
     const uint32_t tP = tS + kPOff;
     const uint32_t tO = tmem + 256 + t * 128 + lane_sel;
-    const int n_t = ntile[t];
     // with an additive bias the scores are moved to the scaled log2 domain when they are read
     // (s <- s * scale_log2 + bias * log2 e), and everything after works with a unit scale
     const float c2 = kMask ? 1.f : a.scale_log2;
+    DropConst dc;
+    if constexpr (kDropout) {
+      dc.add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
+      dc.t_msb = a.drop_threshold >= 128u;
+    }
+    int cnt = 0;                                      // S tiles of my query tile consumed so far
+    FA_TRACE_DECL(trs, 1 + t, tr_cta && (warp & 3) == 0 && lane == 0);
+    for (int n = 0;; ++n) {
+    const int L = next_item(n);
+    if (L < 0) break;
+    const Item it = decode(L);
+    if (!it.valid) continue;
+    const int bidx = it.bidx, head = it.head, sq = it.sq, sk = it.sk, shift = it.shift, m0 = it.m0, q0 = it.q0;
+    const int row = m0 + t * kTileM + r_in_tile;      // row inside the sequence
+    const int n_t = it.ntile[t];
     const uint16_t *mrow = nullptr;
     if (kMask && row < sq)
       mrow = static_cast<const uint16_t *>(a.mask) +
@@ -347,20 +422,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const bool mvec = (sk % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.mask) & 15) == 0);
     const int row_limit = row + shift;                // last visible key when causal
     const int tile_row0 = m0 + t * kTileM;
-
-    DropConst dc;
     uint32_t bh = 0;
-    if constexpr (kDropout) {
-      dc.add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
-      dc.t_msb = a.drop_threshold >= 128u;
-      bh = (uint32_t)((a.batch_base + bidx) * a.h + head);
-    }
+    if constexpr (kDropout) bh = (uint32_t)((a.batch_base + bidx) * a.h + head);
 
     float m_run = -INFINITY, l_run = 0.f;
-    FA_TRACE_DECL(trs, 1 + t, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int j = 0; j < n_t; ++j) {
       FA_TRACE_EV(trs, 10);
-      ptx::mbar_wait(B.s_full + 8 * t, j & 1);
+      ptx::mbar_wait(B.s_full + 8 * t, (cnt + j) & 1);
       ptx::tc_fence_after();
       FA_TRACE_EV(trs, 11);
       uint32_t s[128];
@@ -423,7 +491,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           const float alpha = m_new == -INFINITY ? 1.f : ptx::ex2((m_run - m_new) * c2);
           l_run *= alpha;
           m_run = m_new;
-          ptx::mbar_wait(B.pv_done + 8 * t, (j - 1) & 1);   // O_t holds tiles 0..j-1
+          ptx::mbar_wait(B.pv_done + 8 * t, (cnt + j - 1) & 1);   // O_t holds tiles 0..j-1
           ptx::tc_fence_after();
 #pragma unroll
           for (int c = 0; c < D / 32; ++c) {
@@ -501,7 +569,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const size_t tok = (size_t)(a.cu_q ? q0 : bidx * a.sq) + row;
     uint4 *orow = reinterpret_cast<uint4 *>(static_cast<uint16_t *>(a.out) + (tok * a.h + head) * a.d);
     if (n_t > 0) {
-      ptx::mbar_wait(B.pv_done + 8 * t, (n_t - 1) & 1);
+      ptx::mbar_wait(B.pv_done + 8 * t, (cnt + n_t - 1) & 1);
       ptx::tc_fence_after();
       const float inv = l_run > 0.f ? a.rp_dropout / l_run : 0.f;
 #pragma unroll
@@ -521,6 +589,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           }
         }
       }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.o_free + 8 * t);              // O_t may be overwritten by the next item
     } else if (row_ok) {
 #pragma unroll
       for (int i = 0; i < D / 8; ++i)
@@ -532,6 +602,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           l_run > 0.f ? (log2f(l_run) + m_use * c2) * kLn2 : INFINITY;
     }
     FA_TRACE_EV(trs, 16);
+    cnt += n_t;
+    }   // items
   }
 
   // ---- teardown ----------------------------------------------------------------------
@@ -601,9 +673,28 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
       return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
     attr_set = true;
   }
-  dim3 grid((p.sq + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM), p.h, p.b);
+  a.nqb = (p.sq + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
+  a.n_items = a.nqb * p.h * p.b;
+  a.persistent = packed ? 0 : 1;
+  a.sched = nullptr;
+  int grid = a.n_items;
+  if (a.persistent) {
+    static int sm_count = 0;
+    if (!sm_count) {
+      int dev = 0;
+      if (cudaGetDevice(&dev) != cudaSuccess ||
+          cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+        return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
+    }
+    grid = a.n_items < sm_count ? a.n_items : sm_count;
+    // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
+    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
+      return "cudaMallocAsync(item counter) failed";
+    if (cudaMemsetAsync(a.sched, 0, sizeof(int), stream) != cudaSuccess) return "cudaMemsetAsync(item counter) failed";
+  }
   kern<<<grid, kThreads, C::kSmemBytes, stream>>>(tq, tk, tv, a);
   const cudaError_t err = cudaGetLastError();
+  if (a.sched) cudaFreeAsync(a.sched, stream);
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
 }
 
