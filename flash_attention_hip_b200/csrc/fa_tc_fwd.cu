@@ -43,6 +43,21 @@ constexpr float kRescaleThreshold = 8.0f;  // in log2 units
 // (S4096 D128, build.py --variant): 0 -> 1075, 2 -> 1057, 4 -> 1018, 6 -> 981 TFLOP/s causal: the
 // softmax is bound by the S -> P -> PV -> QK dependency chain and by issue slots, not by MUFU.
 constexpr int kEmuPer8 = FA_EMU_PER8;
+#ifndef FA_FWD_SYNC_GROUPS
+#define FA_FWD_SYNC_GROUPS 2
+#endif
+// Dropout: a scheduling block of the softmax loop = this many groups of (8 exponentials + 5 Philox rounds).
+// ptxas orders instructions freely inside a block and a warp issues in order, so the block size decides how
+// well the integer work hides under the MUFU stream.  Measured on B200 (C3 forward, dropout 0.1):
+// whole tile 710, 4 groups 778, 3 groups 811, 2 groups 818, 1 group 747 TFLOP/s (660 with the draws after S arrived).
+constexpr int kSyncGroups = FA_FWD_SYNC_GROUPS;
+static_assert(FA_PHILOX_ROUNDS == 10, "the forward steps 4 calls x 10 rounds over 8 groups of exponentials");
+#ifndef FA_FWD_APPLY_IN_GROUP
+#define FA_FWD_APPLY_IN_GROUP 0
+#endif
+// AND the keep masks inside the groups (1) or after the half's last exponential (0): 798 against 818 TFLOP/s
+// (tests/cuda/ab_bench.py, interleaved rounds in one process).
+constexpr bool kApplyInGroup = FA_FWD_APPLY_IN_GROUP != 0;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -91,9 +106,12 @@ struct DropConst {
   uint32_t add7;   // (0x80 - (T & 0x7f)) replicated
   bool t_msb;      // T >= 128
 };
-__device__ __forceinline__ void keep_masks(uint32_t w, const DropConst &dc, uint32_t &m01, uint32_t &m23) {
+// bit 7 of each byte of the result: that byte of `w` is < T (the entry is kept)
+__device__ __forceinline__ uint32_t keep_word(uint32_t w, const DropConst &dc) {
   const uint32_t ge7 = (w & 0x7f7f7f7fu) + dc.add7;           // bit7 of each byte: low7 >= T7
-  const uint32_t keep = dc.t_msb ? ~(w & ge7) : ~(w | ge7);   // bit7 of each byte: byte < T
+  return dc.t_msb ? ~(w & ge7) : ~(w | ge7);
+}
+__device__ __forceinline__ void expand_keep(uint32_t keep, uint32_t &m01, uint32_t &m23) {
   // prmt's selector bit 3 replicates the byte's sign; __byte_perm() masks it off, hence asm
   asm("prmt.b32 %0, %1, %1, 0x9988;" : "=r"(m01) : "r"(keep));
   asm("prmt.b32 %0, %1, %1, 0xbbaa;" : "=r"(m23) : "r"(keep));
@@ -426,6 +444,29 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if constexpr (kDropout) bh = (uint32_t)((a.batch_base + bidx) * a.h + head);
 
     float m_run = -INFINITY, l_run = 0.f;
+    // Dropout (csrc/philox_spec.h: one Philox call per 16 columns, one byte per column).  The verdicts do
+    // not depend on S, so they are drawn AHEAD, in the shadow of the MUFU stream: while one 64-column half is
+    // exponentiated, the loop steps the four Philox calls of the half that is handed over next -- (j, 1)
+    // during half 0, (j + 1, 0) during half 1 -- five rounds per 8 exponentials, round-robin over the
+    // calls (four independent chains).  keepw[16 h + w]: bit 7 of each byte = keep, half h of the tile.
+    uint32_t keepw[kDropout ? 32 : 1];
+    uint32_t pc[4][4];
+    auto ctr_init = [&](int q, int j, int hf) {
+      pc[q][0] = (uint32_t)row; pc[q][1] = (uint32_t)(j * (kTileN / 16) + hf * 4 + q); pc[q][2] = bh; pc[q][3] = a.ctr3;
+    };
+    if constexpr (kDropout) {
+      FA_TRACE_EV(trs, 17);
+      if (n_t > 0) {                      // the item's first half: whole calls, before S arrives
+#pragma unroll
+        for (int q = 0; q < 4; ++q) ctr_init(q, 0, 0);
+#pragma unroll
+        for (int r = 0; r < FA_PHILOX_ROUNDS; ++r)
+#pragma unroll
+          for (int q = 0; q < 4; ++q) fa_philox_round(pc[q], a.key0, a.key1, r);
+#pragma unroll
+        for (int w = 0; w < 16; ++w) keepw[w] = ptx::opaque(keep_word(pc[w / 4][w % 4], dc));
+      }
+    }
     for (int j = 0; j < n_t; ++j) {
       FA_TRACE_EV(trs, 10);
       ptx::mbar_wait(B.s_full + 8 * t, (cnt + j) & 1);
@@ -516,10 +557,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       auto exp_half = [&](auto emu_tag, int half) {
         constexpr int kEmu = decltype(emu_tag)::value;
 #pragma unroll
-        for (int c8 = 0; c8 < 64; c8 += 8) {
+        for (int g = 0; g < 8; ++g) {
 #pragma unroll
           for (int pr = 0; pr < 4; ++pr) {
-            const int c = half * 64 + c8 + 2 * pr;
+            const int c = half * 64 + g * 8 + 2 * pr;
             float2 x = __ffma2_rn(ptx::u2f2(s[c], s[c + 1]), c2v, nmv);
             if (2 * pr < kEmu) {
               x = ptx::ex2_poly2(x);
@@ -531,26 +572,48 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             else l01 = __fadd2_rn(l01, x);
             s[c / 2] = pack_pair(x.x, x.y, kBF16);
           }
+          if constexpr (kDropout) {
+            if (kApplyInGroup) {            // this group's 8 entries: keep words 2g, 2g + 1 of the current half
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                uint32_t m01, m23;
+                expand_keep(keepw[half * 16 + 2 * g + u], m01, m23);
+                s[half * 32 + 4 * g + 2 * u] &= m01;
+                s[half * 32 + 4 * g + 2 * u + 1] &= m23;
+              }
+            }
+#pragma unroll
+            for (int k = 5 * g; k < 5 * g + 5; ++k) fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
+            // nvvm would sink the rounds to their use; ptxas would sink them below the tile's last
+            // exponential.  Laundering pins them to this group, __syncwarp() ends ptxas's scheduling block.
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+              for (int i = 0; i < 4; ++i) pc[q][i] = ptx::opaque(pc[q][i]);
+            if (kSyncGroups && g % kSyncGroups == kSyncGroups - 1) __syncwarp();
+          }
         }
       };
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
-        if (need_mask) exp_half(std::integral_constant<int, 0>{}, half);
+        if constexpr (kDropout) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) ctr_init(q, half ? j + 1 : j, 1 - half);
+        }
+        if (kEmuPer8 == 0 || need_mask) exp_half(std::integral_constant<int, 0>{}, half);
         else exp_half(std::integral_constant<int, kEmuPer8>{}, half);
         if constexpr (kDropout) {
-          // csrc/philox_spec.h: one Philox call per 16 columns, one byte per column
+          if (!kApplyInGroup) {
 #pragma unroll
-          for (int cb = half * 4; cb < half * 4 + 4; ++cb) {
-            const fa_philox4_t rnd = fa_philox4x32((uint32_t)row, (uint32_t)(col0 / 16 + cb), bh, a.ctr3,
-                                                   a.key0, a.key1);
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
+            for (int w = half * 16; w < half * 16 + 16; ++w) {
               uint32_t m01, m23;
-              keep_masks(rnd.v[w], dc, m01, m23);
-              s[cb * 8 + w * 2] &= m01;
-              s[cb * 8 + w * 2 + 1] &= m23;
+              expand_keep(keepw[w], m01, m23);
+              s[w * 2] &= m01;
+              s[w * 2 + 1] &= m23;
             }
           }
+#pragma unroll
+          for (int w = 0; w < 16; ++w) keepw[(1 - half) * 16 + w] = keep_word(pc[w / 4][w % 4], dc);
         }
         // hand P over in halves: O += P[:, :64] V[:64] starts while the second half is exponentiated
         uint32_t(&ph)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[half * 32]);

@@ -47,22 +47,22 @@
 
 typedef struct { uint32_t v[4]; } fa_philox4_t;
 
+/* Round r (0-based) of Philox-4x32 on the counter c[0..3] with the ORIGINAL key (k0, k1): the round key
+ * is (k0 + r*W0, k1 + r*W1).  Kernels that interleave several calls step through this directly. */
+FA_HD void fa_philox_round(uint32_t c[4], uint32_t k0, uint32_t k1, int r) {
+  const uint64_t p0 = (uint64_t)FA_PHILOX_M0 * c[0];
+  const uint64_t p1 = (uint64_t)FA_PHILOX_M1 * c[2];
+  const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ (k0 + (uint32_t)r * FA_PHILOX_W0);
+  const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ (k1 + (uint32_t)r * FA_PHILOX_W1);
+  c[0] = n0; c[1] = (uint32_t)p1; c[2] = n2; c[3] = (uint32_t)p0;
+}
+
 /* Philox-4x32 with FA_PHILOX_ROUNDS rounds. */
 FA_HD fa_philox4_t fa_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                  uint32_t k0, uint32_t k1) {
-  for (int r = 0; r < FA_PHILOX_ROUNDS; ++r) {
-    const uint64_t p0 = (uint64_t)FA_PHILOX_M0 * c0;
-    const uint64_t p1 = (uint64_t)FA_PHILOX_M1 * c2;
-    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
-    const uint32_t n1 = (uint32_t)p1;
-    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
-    const uint32_t n3 = (uint32_t)p0;
-    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-    k0 += FA_PHILOX_W0;
-    k1 += FA_PHILOX_W1;
-  }
   fa_philox4_t out;
   out.v[0] = c0; out.v[1] = c1; out.v[2] = c2; out.v[3] = c3;
+  for (int r = 0; r < FA_PHILOX_ROUNDS; ++r) fa_philox_round(out.v, k0, k1, r);
   return out;
 }
 
