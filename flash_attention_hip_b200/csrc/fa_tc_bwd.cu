@@ -29,9 +29,13 @@ namespace fa {
 
 namespace {
 
+#ifndef FA_BWD_SYNC_GROUPS
+#define FA_BWD_SYNC_GROUPS 2
+#endif
 #ifndef FA_BWD_DRAIN_REGS
 #define FA_BWD_DRAIN_REGS 144
 #endif
+constexpr int kBwdSyncGroups = FA_BWD_SYNC_GROUPS;   // dropout: scheduling block = this many groups of 8 exponentials + 5 Philox rounds
 constexpr int kT = 128;            // tile edge: keys per CTA tile, queries per inner tile
 constexpr int kThreads = 512;
 constexpr int kMmaWarp = 8, kLoadWarp = 9, kDrainWarp0 = 12;
@@ -110,6 +114,17 @@ __device__ __forceinline__ uint32_t keep_bits16(const fa_philox4_t &r, uint32_t 
     bits |= nib << (4 * w);
   }
   return bits;
+}
+
+// AND-mask of packed pair c (entries 2c, 2c + 1 of 32) from a word of keep bits (bit e = keep entry e).
+// wk[k] = bits << (7 - k) puts entry k + 8m at the top of byte m; PRMT's sign-replicate mode (selector bit
+// 3) then expands two such bytes to 16 bits each: one PRMT + one AND per pair, 8 shifts per 32 entries.
+__device__ __forceinline__ uint32_t pair_mask(const uint32_t (&wk)[8], int pair) {
+  const int e = 2 * pair, k = e % 8, m = e / 8;
+  const uint32_t sel = (8u + m) * 0x0011u + (12u + m) * 0x1100u;   // bytes {a.m, a.m, b.m, b.m}, sign-replicated
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(wk[k]), "r"(wk[k + 1]), "r"(sel));   // sel folds to an immediate
+  return d;
 }
 
 // One butterfly stage of four 16x16 bit transposes (two per word) across the lanes of each
@@ -444,6 +459,30 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       t_msb = a.drop_threshold >= 128u;
     }
 
+    // Dropout keep bits for my 64 (query, key) pairs per iteration (csrc/philox_spec.h): the lanes of a
+    // half-warp share the key block, so each lane draws the 16 bytes of ONE query row per 16-row block
+    // (four calls) and the rows are exchanged.  The draws do not depend on S^T: iteration it + 1's four
+    // calls are stepped under iteration it's exponentials (five rounds per 8 MUFU, as in the forward).
+    uint32_t pc[4][4];
+    auto ctr_init = [&](int it_) {
+      const int hq_ = hk * group + it_ / n_i, i_ = q_tile_of(it_);
+      const uint32_t bh_ = (uint32_t)((a.batch_base + bidx) * a.h + hq_);
+#pragma unroll
+      for (int blk = 0; blk < 4; ++blk) {
+        pc[blk][0] = (uint32_t)(i_ * kT + w * 64 + blk * 16 + (lane & 15));
+        pc[blk][1] = (uint32_t)(n_abs >> 4); pc[blk][2] = bh_; pc[blk][3] = a.ctr3;
+      }
+    };
+    if constexpr (kDropout) {
+      if (n_it > 0) {
+        ctr_init(0);
+#pragma unroll
+        for (int r = 0; r < FA_PHILOX_ROUNDS; ++r)
+#pragma unroll
+          for (int blk = 0; blk < 4; ++blk) fa_philox_round(pc[blk], a.key0, a.key1, r);
+      }
+    }
+
     FA_TRACE_DECL(trc, 2 + w, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
@@ -456,12 +495,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // block, so each lane draws the 16 bytes of ONE query row and the rows are exchanged.
       uint32_t keep_lo = 0xffffffffu, keep_hi = 0xffffffffu;
       if constexpr (kDropout) {
-        const uint32_t bh = (uint32_t)((a.batch_base + bidx) * a.h + hq);
+        // pc[blk] holds the finished Philox words of query row q_base + 16 blk + lane % 16 for THIS iteration:
+        // drawn whole before the loop (it == 0) or stepped under the previous iteration's exponentials
         uint32_t w01 = 0, w23 = 0;        // bit 16*b + k: keep(query q_base + 16*b' + lane%16, key k of my block)
 #pragma unroll
         for (int blk = 0; blk < 4; ++blk) {
-          const fa_philox4_t rnd = fa_philox4x32((uint32_t)(q_base + blk * 16 + (lane & 15)),
-                                                 (uint32_t)(n_abs >> 4), bh, a.ctr3, a.key0, a.key1);
+          fa_philox4_t rnd;
+#pragma unroll
+          for (int x = 0; x < 4; ++x) rnd.v[x] = pc[blk][x];
           const uint32_t mine = keep_bits16(rnd, add7, t_msb);
           if (blk < 2) w01 |= mine << (16 * blk);
           else w23 |= mine << (16 * (blk - 2));
@@ -509,6 +550,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         cs = 1.f;
       }
       const float2 c2v = make_float2(cs, cs);
+      if constexpr (kDropout) ctr_init(it + 1);           // (one wasted draw after the last iteration)
 #pragma unroll
       for (int c = 0; c < 64; c += 4) {
         const float4 nl = ld_shared_f32x4(stat + 4 * c);                  // -lse2 of 4 query columns
@@ -516,6 +558,21 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         float2 y = __ffma2_rn(make_float2(p[c + 2], p[c + 3]), c2v, make_float2(nl.z, nl.w));
         p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
         p[c + 2] = ptx::ex2(y.x); p[c + 3] = ptx::ex2(y.y);
+        if constexpr (kDropout) {
+          if (c % 8 == 4) {               // a group = 8 exponentials + 5 Philox rounds, round-robin over the calls
+            const int g = c / 8;
+#pragma unroll
+            for (int k = 5 * g; k < 5 * g + 5; ++k) fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
+            // nvvm would sink the rounds to their use and ptxas below the last exponential (a warp issues in
+            // order: they would run after the MUFU stream, not under it): laundering pins them to this
+            // group, __syncwarp() ends ptxas's scheduling block
+#pragma unroll
+            for (int blk = 0; blk < 4; ++blk)
+#pragma unroll
+              for (int x2 = 0; x2 < 4; ++x2) pc[blk][x2] = ptx::opaque(pc[blk][x2]);
+            if (kBwdSyncGroups && g % kBwdSyncGroups == kBwdSyncGroups - 1) __syncwarp();
+          }
+        }
       }
       FA_TRACE_EV(trc, 31);
       if (diag || ragged_k) {                            // CTA/warp-uniform: only diagonal and last key tiles
@@ -526,14 +583,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       {
         uint32_t pk[32];
 #pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          float lo = p[2 * c], hi = p[2 * c + 1];
-          if constexpr (kDropout) {
-            const uint32_t kb = c < 16 ? keep_lo >> (2 * c) : keep_hi >> (2 * c - 32);
-            if (!(kb & 1u)) lo = 0.f;
-            if (!(kb & 2u)) hi = 0.f;
+        for (int c = 0; c < 32; ++c) pk[c] = pack2(p[2 * c], p[2 * c + 1], kBF16);
+        if constexpr (kDropout) {
+#pragma unroll
+          for (int hw = 0; hw < 2; ++hw) {
+            uint32_t wk[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) wk[k] = (hw ? keep_hi : keep_lo) << (7 - k);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) pk[16 * hw + c] &= pair_mask(wk, c);
           }
-          pk[c] = pack2(lo, hi, kBF16);
         }
         FA_TRACE_EV(trc, 32);
         ptx::tmem_st_x32(tS + lane_sel + w * 64, pk);     // P^T half w lives in columns [64w, 64w+32)
