@@ -32,10 +32,15 @@ namespace {
 #ifndef FA_BWD_SYNC_GROUPS
 #define FA_BWD_SYNC_GROUPS 2
 #endif
+#ifndef FA_BWD_EMU_EVERY
+#define FA_BWD_EMU_EVERY 0
+#endif
 #ifndef FA_BWD_DRAIN_REGS
 #define FA_BWD_DRAIN_REGS 144
 #endif
 constexpr int kBwdSyncGroups = FA_BWD_SYNC_GROUPS;   // dropout: scheduling block = this many groups of 8 exponentials + 5 Philox rounds
+// Every n-th group of four exponentials computes one pair on the FMA pipe instead of MUFU (0 = never).
+constexpr int kBwdEmuEvery = FA_BWD_EMU_EVERY;
 constexpr int kT = 128;            // tile edge: keys per CTA tile, queries per inner tile
 constexpr int kThreads = 512;
 constexpr int kMmaWarp = 8, kLoadWarp = 9, kDrainWarp0 = 12;
@@ -557,7 +562,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         float2 x = __ffma2_rn(make_float2(p[c], p[c + 1]), c2v, make_float2(nl.x, nl.y));
         float2 y = __ffma2_rn(make_float2(p[c + 2], p[c + 3]), c2v, make_float2(nl.z, nl.w));
         p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
-        p[c + 2] = ptx::ex2(y.x); p[c + 3] = ptx::ex2(y.y);
+        if (kBwdEmuEvery && (c / 4) % kBwdEmuEvery == 0) {   // this pair on the FMA pipe (ptx::ex2_poly2)
+          y = ptx::ex2_poly2(y);
+          p[c + 2] = y.x; p[c + 3] = y.y;
+        } else {
+          p[c + 2] = ptx::ex2(y.x); p[c + 3] = ptx::ex2(y.y);
+        }
         if constexpr (kDropout) {
           if (c % 8 == 4) {               // a group = 8 exponentials + 5 Philox rounds, round-robin over the calls
             const int g = c / 8;
@@ -606,16 +616,25 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::mbar_wait(B.dp_full, it & 1);
       ptx::tc_fence_after();
       FA_TRACE_EV(trc, 14);
-      uint32_t ds[32];
+      // GEMMs (5),(4) of it-1 have read dS^T: q_empty is committed after the later of the two (dK).  Long
+      // done by now, so waiting here (not after the math) costs nothing and lets each 16-column chunk of
+      // dS^T leave for shared memory as soon as it is computed.
+      if (it > 0) ptx::mbar_wait(B.q_empty + 8 * ((it - 1) & 1), ((it - 1) >> 1) & 1);
+      FA_TRACE_EV(trc, 16);
       {
-        uint32_t dp[32];
+        // dP^T comes in four 16-column chunks; chunk q + 1 is in flight while chunk q is worked on
+        const uint32_t rowp = sbase + C::kDS + w * C::kSub + n * 128;
+        uint32_t dpb[2][16];
+        ptx::tmem_ld_x16(tDP + lane_sel + w * 64, dpb[0]);
+        ptx::tmem_wait_ld();
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          ptx::tmem_ld_x32(tDP + lane_sel + w * 64 + half * 32, dp);
-          ptx::tmem_wait_ld();
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint32_t(&dp)[16] = dpb[q4 & 1];
+          if (q4 < 3) ptx::tmem_ld_x16(tDP + lane_sel + w * 64 + (q4 + 1) * 16, dpb[(q4 + 1) & 1]);
+          uint32_t ds[8];
 #pragma unroll
-          for (int c = 0; c < 32; c += 4) {
-            const int cq = half * 32 + c;
+          for (int c = 0; c < 16; c += 4) {
+            const int cq = q4 * 16 + c;
             float2 g01 = ptx::u2f2(dp[c], dp[c + 1]), g23 = ptx::u2f2(dp[c + 2], dp[c + 3]);
             if constexpr (kDropout) {
               const uint32_t kb = cq < 32 ? keep_lo >> cq : keep_hi >> (cq - 32);
@@ -627,21 +646,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const float4 nd = ld_shared_f32x4(stat + 512 + 4 * cq);        // -D of 4 query columns
             const float2 e01 = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(g01, make_float2(nd.x, nd.y)));
             const float2 e23 = __fmul2_rn(make_float2(p[cq + 2], p[cq + 3]), __fadd2_rn(g23, make_float2(nd.z, nd.w)));
-            ds[cq / 2] = pack2(e01.x, e01.y, kBF16);
-            ds[cq / 2 + 1] = pack2(e23.x, e23.y, kBF16);
+            ds[c / 2] = pack2(e01.x, e01.y, kBF16);
+            ds[c / 2 + 1] = pack2(e23.x, e23.y, kBF16);
           }
+#pragma unroll
+          for (int k = 0; k < 2; ++k)
+            st_shared_v4(rowp + (((2 * q4 + k) ^ (n & 7)) << 4), ds[4 * k], ds[4 * k + 1], ds[4 * k + 2], ds[4 * k + 3]);
+          if (q4 < 3) ptx::tmem_wait_ld();
         }
       }
       FA_TRACE_EV(trc, 15);
-      // GEMMs (5),(4) of it-1 have read dS^T: q_empty is committed after the later of the two (dK)
-      if (it > 0) ptx::mbar_wait(B.q_empty + 8 * ((it - 1) & 1), ((it - 1) >> 1) & 1);
-      FA_TRACE_EV(trc, 16);
-      {
-        const uint32_t rowp = sbase + C::kDS + w * C::kSub + n * 128;
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          st_shared_v4(rowp + ((k ^ (n & 7)) << 4), ds[4 * k], ds[4 * k + 1], ds[4 * k + 2], ds[4 * k + 3]);
-      }
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(B.ds_ready);
