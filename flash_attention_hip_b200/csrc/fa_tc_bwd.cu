@@ -58,13 +58,14 @@ struct Cfg {
   static constexpr uint32_t kDQ = kDS + 2 * kSub;     // 2 x 16 KB fp32 staging blocks
   static constexpr uint32_t kStat = kDQ + 2 * 16384;  // 2 stages x {lse2[128], D[128]} fp32
   static constexpr uint32_t kBar = kStat + 2 * 1024;
-  static constexpr uint32_t kNumBars = 16;
-  static constexpr uint32_t kDesc = kBar + 256;        // 4 x 128 B tensor-map staging (packed inputs)
-  static constexpr uint32_t kBytes = kDesc + 4 * 128;
+  static constexpr uint32_t kNumBars = 20;
+  static constexpr uint32_t kDesc = kBar + 256;        // 6 x 128 B tensor-map staging (packed inputs)
+  static constexpr uint32_t kBytes = kDesc + 6 * 128;
+  static_assert(kBytes <= 232448, "over the 227 KB a CTA may ask for");
   static_assert(kBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
 
-__device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][4];
+__device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][6];
 
 struct BwdArgs {
   void *dk, *dv;
@@ -79,6 +80,9 @@ struct BwdArgs {
   float scale, scale_log2, rp_dropout;
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
+  int nkt, n_items;      // key tiles per sequence (dense: of sk; packed: of the longest); items = nkt * hk * b
+  int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
+  int *sched;            // global item counter (stream-ordered temporary, zeroed before the launch)
 };
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi, bool bf16) {
@@ -153,13 +157,14 @@ namespace {
 
 struct BwdBars {
   uint32_t kv_full, q_full /*[2]*/, q_empty /*[2]*/, do_full, do_empty, s_full, dp_full, p_ready, ds_ready,
-      dq_full, dq_drained, acc_done;
+      dq_full, dq_drained, acc_done, epi_tmem_free, epi_smem_free, sched_full /*[2]*/, sched_empty /*[2]*/;
 };
 
 template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
+              const __grid_constant__ CUtensorMap tmap_dk, const __grid_constant__ CUtensorMap tmap_dv,
               const BwdArgs a) {
   using C = Cfg<D>;
   // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
@@ -176,31 +181,54 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   // elect.sync is issued without a per-instruction election loop (see fa_tc_fwd.cu)
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
-  // ---- problem coordinates ---------------------------------------------------------
-  const int j = blockIdx.x, hk = blockIdx.y, bidx = blockIdx.z;
-  int sq = a.sq, sk = a.sk, qrow0 = 0, krow0 = 0, bcoord = bidx;   // TMA row origin / batch coordinate
-  size_t qtok0 = (size_t)bidx * a.sq, ktok0 = (size_t)bidx * a.sk; // first token of this sequence
-  if (a.cu_q) {
-    qrow0 = a.cu_q[bidx]; krow0 = a.cu_k[bidx];
-    sq = a.cu_q[bidx + 1] - qrow0; sk = a.cu_k[bidx + 1] - krow0;
-    qtok0 = (size_t)qrow0; ktok0 = (size_t)krow0; bcoord = 0;
-  }
-  if (j * kT >= sk) return;                    // packed: this sequence has no such key tile
+  // ---- work items -----------------------------------------------------------------------
+  // One item = one 128-key tile of one (batch, kv head): dK_j / dV_j stay in tensor memory while the item's
+  // loop walks the group's query heads and the query tiles that see the key tile.  Linear order: key tiles
+  // fastest (causal: the heaviest first).  Dense inputs: one persistent CTA per SM pulls items from a global
+  // counter, and its TMA / MMA / drain warps run ahead into the next item while the compute warps write dK
+  // and dV out (a CTA's start -- DRAM latency of the first loads -- and its 64 KB epilogue on a ~26 B/clk
+  // store port were ~8000 of ~70000 cycles per item, traced).  Packed inputs and ordered dQ: one item per CTA.
+  struct Item {
+    int j, hk, bidx, sq, sk, qrow0, krow0, bcoord, shift, i_min, n_i, n_it;
+    size_t qtok0, ktok0;
+    bool valid;
+  };
   const int group = a.h / a.hk;
-  const int shift = sk - sq;                   // causal: key n visible to row r iff n <= r + shift
-  const int nqt = (sq + kT - 1) / kT;          // query tiles of this sequence
-  int i_min = 0;
-  if (a.causal) {
-    const int first_row = j * kT - shift;      // first query row that sees key j*128
-    i_min = first_row <= 0 ? 0 : first_row / kT;
-  }
-  const int n_i = max(0, nqt - i_min);         // query tiles per head
-  const int n_it = n_i * group;                // inner iterations: (head in group, query tile)
+  auto decode = [&](int L) {
+    Item I;
+    I.j = L % a.nkt; I.hk = (L / a.nkt) % a.hk; I.bidx = L / (a.nkt * a.hk);
+    I.sq = a.sq; I.sk = a.sk; I.qrow0 = 0; I.krow0 = 0; I.bcoord = I.bidx;   // TMA row origin / batch coordinate
+    I.qtok0 = (size_t)I.bidx * a.sq; I.ktok0 = (size_t)I.bidx * a.sk;        // first token of this sequence
+    if (a.cu_q) {
+      I.qrow0 = a.cu_q[I.bidx]; I.krow0 = a.cu_k[I.bidx];
+      I.sq = a.cu_q[I.bidx + 1] - I.qrow0; I.sk = a.cu_k[I.bidx + 1] - I.krow0;
+      I.qtok0 = (size_t)I.qrow0; I.ktok0 = (size_t)I.krow0; I.bcoord = 0;
+    }
+    I.valid = I.j * kT < I.sk;                   // packed: this sequence may have no such key tile
+    I.shift = I.sk - I.sq;                       // causal: key n visible to row r iff n <= r + shift
+    const int nqt = (I.sq + kT - 1) / kT;        // query tiles of this sequence
+    I.i_min = 0;
+    if (a.causal) {
+      const int first_row = I.j * kT - I.shift;  // first query row that sees key j*128
+      I.i_min = first_row <= 0 ? 0 : first_row / kT;
+    }
+    I.n_i = max(0, nqt - I.i_min);               // query tiles per head
+    I.n_it = I.n_i * group;                      // inner iterations: (head in group, query tile)
+    return I;
+  };
+  if (!a.persistent && !decode((int)blockIdx.x).valid) return;
   // Query tile of inner iteration `it`.  Ordered (deterministic) dQ walks the tiles from the last one
   // down: every key-tile CTA of a causal problem then starts on the same query tile and the turns
   // form a pipeline, instead of CTA j first waiting for the diagonal tile of all its predecessors.
   constexpr bool descending = kOrdered;
-  auto q_tile_of = [&](int it) { return descending ? i_min + n_i - 1 - it % n_i : i_min + it % n_i; };
+#define FA_ITEM_LOCALS(I)                                                                                      \
+  const int j = (I).j, hk = (I).hk, bidx = (I).bidx, sq = (I).sq, sk = (I).sk, qrow0 = (I).qrow0,              \
+            krow0 = (I).krow0, bcoord = (I).bcoord, shift = (I).shift, i_min = (I).i_min, n_i = (I).n_i,      \
+            n_it = (I).n_it;                                                                                   \
+  const size_t qtok0 = (I).qtok0, ktok0 = (I).ktok0;                                                           \
+  auto q_tile_of = [&](int it_) { return descending ? i_min + n_i - 1 - it_ % n_i : i_min + it_ % n_i; };      \
+  (void)j; (void)hk; (void)bidx; (void)sq; (void)sk; (void)qrow0; (void)krow0; (void)bcoord; (void)shift;      \
+  (void)i_min; (void)qtok0; (void)ktok0; (void)q_tile_of
 
   // ---- barriers, tensor memory --------------------------------------------------------
   const uint32_t bar0 = sbase + C::kBar;
@@ -208,7 +236,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   B.kv_full = bar0;          B.q_full = bar0 + 8;      B.q_empty = bar0 + 24;   B.do_full = bar0 + 40;
   B.do_empty = bar0 + 48;    B.s_full = bar0 + 56;     B.dp_full = bar0 + 64;   B.p_ready = bar0 + 72;
   B.ds_ready = bar0 + 80;    B.dq_full = bar0 + 88;    B.dq_drained = bar0 + 96; B.acc_done = bar0 + 104;
+  B.epi_tmem_free = bar0 + 112; B.epi_smem_free = bar0 + 120; B.sched_full = bar0 + 128; B.sched_empty = bar0 + 144;
+  static_assert(C::kNumBars >= 20, "barrier block too small");
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem_raw + C::kBar + C::kNumBars * 8);
+  volatile int *sched_item = reinterpret_cast<volatile int *>(tmem_slot + 2);   // [2]
 
   if (threadIdx.x == 0) {
     ptx::mbar_init(B.kv_full, 1);
@@ -219,6 +250,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::mbar_init(B.p_ready, 256);   ptx::mbar_init(B.ds_ready, 256);
     ptx::mbar_init(B.dq_full, 1);     ptx::mbar_init(B.dq_drained, 128);
     ptx::mbar_init(B.acc_done, 1);
+    ptx::mbar_init(B.epi_tmem_free, 128);  ptx::mbar_init(B.epi_smem_free, 1);   // (epi_smem_free: unused)
+    for (int t = 0; t < 2; ++t) {
+      ptx::mbar_init(B.sched_full + 8 * t, 1);
+      ptx::mbar_init(B.sched_empty + 8 * t, 1 + 128 + 256);    // MMA lane, drain warps, compute warps
+    }
     ptx::fence_mbar_init();
   }
   if (warp == kLoadWarp && lane == 0) {
@@ -236,8 +272,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 384;
 
 #ifdef FA_TRACE
-  const bool tr_cta = blockIdx.x == gridDim.x / 2 && blockIdx.y == 0 && blockIdx.z == gridDim.z / 2;
+  const bool tr_cta = blockIdx.x == gridDim.x / 2;
 #endif
+  // Consumers of the item queue (MMA lane, drain and compute threads): item number n of this CTA, or -1.
+  auto next_item = [&](int n) {
+    const int slot = n & 1;
+    ptx::mbar_wait(B.sched_full + 8 * slot, (n >> 1) & 1);
+    const int L = sched_item[slot];
+    ptx::mbar_arrive(B.sched_empty + 8 * slot);
+    return L;
+  };
   if (warp >= 8 && warp < 12) {
     // =========================== producer warpgroup ======================================
     ptx::setmaxnreg_dec<32>();
@@ -245,7 +289,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // ---- TMA producer; all 32 lanes stage LSE / D -----------------------------------------
       const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v, *mdo = &tmap_do;
       if (a.cu_q) {
-        // packed inputs: rows past this sequence's end must read as zero, not as the next sequence
+        // packed inputs (one item per CTA): rows past this sequence's end must read as zero, not as the next sequence
+        const Item I0 = decode((int)blockIdx.x);
+        const int qrow0 = I0.qrow0, krow0 = I0.krow0, sq = I0.sq, sk = I0.sk;
         const uint32_t sm = ptx::smid();
         if (sm >= (uint32_t)ptx::kMaxSm) __trap();
         const uint32_t d0 = sbase + C::kDesc;
@@ -255,6 +301,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         mk = ptx::patch_rows(tmap_k, &g_bwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(krow0 + sk), lane);
         mv = ptx::patch_rows(tmap_v, &g_bwd_slots[sm][3], d0 + 384, g0 + 384, (uint32_t)(krow0 + sk), lane);
       }
+      int g0 = 0;                                      // iterations of the items before this one (ring stages, phases)
+      for (int n = 0;; ++n) {
+      // ---- scheduler: lane 0 takes the next item and publishes it to the other roles ----
+      int L = 0;
+      if (lane == 0) {
+        const int slot = n & 1;
+        if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
+        L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
+        if (L >= a.n_items) L = -1;
+        sched_item[slot] = L;
+        ptx::mbar_arrive(B.sched_full + 8 * slot);
+      }
+      L = __shfl_sync(0xffffffffu, L, 0);
+      if (L < 0) break;
+      const Item I = decode(L);
+      FA_ITEM_LOCALS(I);
+      if (n >= 1) ptx::mbar_wait(B.acc_done, (n - 1) & 1);   // the previous item's MMAs have read K and V
       if (lane == 0) {
         ptx::mbar_arrive_expect_tx(B.kv_full, 2 * C::kTile);
         for (int c = 0; c < D / 64; ++c) {
@@ -264,8 +327,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       for (int it = 0; it < n_it; ++it) {
         const int hq = hk * group + it / n_i, i = q_tile_of(it);
-        const int s = it & 1;
-        if (it >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((it >> 1) - 1) & 1);
+        const int g = g0 + it, s = g & 1;
+        if (g >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((g >> 1) - 1) & 1);
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.q_full + 8 * s, C::kTile);
           for (int c = 0; c < D / 64; ++c)
@@ -288,13 +351,15 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(B.q_full + 8 * s);
         }
-        if (it >= 1) ptx::mbar_wait(B.do_empty, (it - 1) & 1);
+        if (g >= 1) ptx::mbar_wait(B.do_empty, (g - 1) & 1);
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.do_full, C::kTile);
           for (int c = 0; c < D / 64; ++c)
             ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, mdo, B.do_full, c * 64, hq, qrow0 + i * kT, bcoord);
         }
       }
+      g0 += n_it;
+      }   // items
     } else if (warp == kMmaWarp && ptx::elect_one()) {
       // ---- MMA issuer -----------------------------------------------------------------------
       constexpr uint32_t fmt = kBF16 ? ptx::kFmtBF16 : ptx::kFmtF16;
@@ -313,28 +378,36 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       };
       FA_TRACE_DECL(tr, 0, tr_cta);
-      ptx::mbar_wait(B.kv_full, 0);
+      int g0 = 0;
+      for (int n = 0;; ++n) {
+      const int L = next_item(n);
+      if (L < 0) break;
+      const Item I = decode(L);
+      FA_ITEM_LOCALS(I);
+      ptx::mbar_wait(B.kv_full, n & 1);
       ptx::tc_fence_after();
       if (n_it > 0) {
-        ptx::mbar_wait(B.q_full, 0);
+        ptx::mbar_wait(B.q_full + 8 * (g0 & 1), (g0 >> 1) & 1);
         ptx::tc_fence_after();
-        gemm_kk(tS, sbase >> 4, C::kK, sbase >> 4, C::kQ);                         // (1) S^T(0)
+        gemm_kk(tS, sbase >> 4, C::kK, (sbase >> 4) + (g0 & 1) * (C::kTile >> 4), C::kQ);   // (1) S^T(0)
         ptx::mma_commit(B.s_full);
       }
       for (int it = 0; it < n_it; ++it) {
-        const int s = it & 1;
+        const int g = g0 + it, s = g & 1;
         // descriptors are rebuilt from this laundered base every iteration (see smem_desc_at)
         const uint32_t b16 = ptx::opaque(sbase >> 4);
         const uint32_t q16 = b16 + s * (C::kTile >> 4), qn16 = b16 + (s ^ 1) * (C::kTile >> 4);
         FA_TRACE_EV(tr, 1);
-        ptx::mbar_wait(B.do_full, it & 1);
+        ptx::mbar_wait(B.do_full, g & 1);
         FA_TRACE_EV(tr, 2);
-        if (it > 0) ptx::mbar_wait(B.dq_drained, (it - 1) & 1);           // dP^T shares TMEM with dQ
+        if (g > 0) ptx::mbar_wait(B.dq_drained, (g - 1) & 1);             // dP^T shares TMEM with dQ
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 3);
         gemm_kk(tDP, b16, C::kV, b16, C::kDO);                               // (2) dP^T(it)
         ptx::mma_commit(B.dp_full);
-        ptx::mbar_wait(B.p_ready, it & 1);
+        ptx::mbar_wait(B.p_ready, g & 1);
+        // the first dV / dK MMAs of an item overwrite the accumulators: the previous item's epilogue must have read them
+        if (it == 0 && n >= 1) ptx::mbar_wait(B.epi_tmem_free, (n - 1) & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 4);
 #pragma unroll
@@ -343,13 +416,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
                       ptx::smem_desc_at(hi_mn, b16, C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
         ptx::mma_commit(B.do_empty);
         if (it + 1 < n_it) {
-          ptx::mbar_wait(B.q_full + 8 * (s ^ 1), ((it + 1) >> 1) & 1);
+          ptx::mbar_wait(B.q_full + 8 * (s ^ 1), ((g + 1) >> 1) & 1);
           ptx::tc_fence_after();
           gemm_kk(tS, b16, C::kK, qn16, C::kQ);                          // (1) S^T(it+1)
           ptx::mma_commit(B.s_full);
         }
         FA_TRACE_EV(tr, 5);
-        ptx::mbar_wait(B.ds_ready, it & 1);
+        ptx::mbar_wait(B.ds_ready, g & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 6);
         // dQ first: it heads the longest dependency chain of the loop (dQ -> drain -> dP^T(it+1) -> dS
@@ -368,6 +441,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::mma_commit(B.q_empty + 8 * s);
       }
       ptx::mma_commit(B.acc_done);
+      g0 += n_it;
+      }   // items
     }
   } else if (warp >= kDrainWarp0) {
     // =========================== dQ drain warpgroup ======================================
@@ -380,13 +455,31 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const uint32_t lane_sel = (uint32_t)(dw * 32) << 16;
     const bool leader = (warp == kDrainWarp0 && lane == 0);
     uint32_t cc = 0;                                   // running 16 KB block counter (staging ring of 2)
+    const CUtensorMap *mdk = &tmap_dk, *mdv = &tmap_dv;
+    if (a.cu_q && warp == kDrainWarp0) {
+      // packed inputs (one item per CTA): rows past this sequence's end belong to the next sequence -- clip the stores
+      const Item I0 = decode((int)blockIdx.x);
+      const uint32_t sm = ptx::smid();
+      if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+      const uint32_t d0 = sbase + C::kDesc;
+      uint8_t *gen0 = smem_raw + C::kDesc;
+      mdk = ptx::patch_rows(tmap_dk, &g_bwd_slots[sm][4], d0 + 512, gen0 + 512, (uint32_t)(I0.krow0 + I0.sk), lane);
+      mdv = ptx::patch_rows(tmap_dv, &g_bwd_slots[sm][5], d0 + 640, gen0 + 640, (uint32_t)(I0.krow0 + I0.sk), lane);
+    }
+    if (leader) { ptx::prefetch_tensormap(mdk); ptx::prefetch_tensormap(mdv); }
     FA_TRACE_DECL(trd, 1, tr_cta && leader);
+    int g0 = 0;
+    for (int n = 0;; ++n) {
+    const int L = next_item(n);
+    if (L < 0) break;
+    const Item I = decode(L);
+    FA_ITEM_LOCALS(I);
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
       float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * a.nblk) * 4096;
       FA_TRACE_EV(trd, 20);
-      ptx::mbar_wait(B.dq_full, it & 1);
+      ptx::mbar_wait(B.dq_full, (g0 + it) & 1);
       ptx::tc_fence_after();
       FA_TRACE_EV(trd, 21);
       // kEarlyDrain: the whole dQ tile -> registers first, so dP^T(it+1) may reuse the TMEM columns at once
@@ -446,15 +539,64 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(j + 1) : "memory");
       }
     }
+    // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
+    // A drain thread owns one ROW of dK / dV (TMEM lane = key row).  The tiles leave like the dQ blocks do:
+    // 64 columns x 128 rows are parked in a 16 KB staging block in the tensor map's 128-byte-swizzled box
+    // layout and ONE bulk tensor store sends the box (rows past the sequence end and columns past head_size
+    // are clipped by the map) -- while the compute warps are already in the next item.  (They used to stage
+    // both tiles in the Q ring and write them out themselves: ~5000 cycles per item on a store port the dQ
+    // tiles keep 64 % busy.  One small bulk copy per row was measured too: ~18 cycles per copy, 18800 per item.)
+    ptx::mbar_wait(B.acc_done, n & 1);
+    ptx::tc_fence_after();
+    FA_TRACE_EV(trd, 23);
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      const float mul = which ? a.scale : a.rp_dropout;
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c) {
+        const uint32_t buf = sbase + C::kDQ + (cc & 1) * 16384;
+        if (leader && cc >= 2) ptx::tma_store_wait_read<1>();   // the block that used `buf` has been read
+        ptx::named_bar_sync(1, 128);
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t v[32];
+          if (n_it > 0) {
+            ptx::tmem_ld_x32((which ? tDK : tDV) + lane_sel + c * 64 + hf * 32, v);
+            ptx::tmem_wait_ld();
+          } else {
+#pragma unroll
+            for (int x = 0; x < 32; ++x) v[x] = 0;
+          }
+          if (which == 1 && c == D / 64 - 1 && hf == 1) {     // dK / dV read: the next item's MMAs may overwrite them
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(B.epi_tmem_free);
+          }
+#pragma unroll
+          for (int x = 0; x < 4; ++x)
+            st_shared_v4(buf + r * 128 + (((hf * 4 + x) ^ (r & 7)) << 4),
+                         pack2(__uint_as_float(v[8 * x]) * mul, __uint_as_float(v[8 * x + 1]) * mul, kBF16),
+                         pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16),
+                         pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16),
+                         pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16));
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::named_bar_sync(1, 128);
+        if (leader) {
+          if (c * 64 < a.d) ptx::tma_store_4d(which ? mdk : mdv, buf, c * 64, hk, krow0 + j * kT, bcoord);
+          ptx::tma_store_commit();
+        }
+        ++cc;
+      }
+    }
+    FA_TRACE_EV(trd, 24);
+    g0 += n_it;
+    }   // items
     if (leader) ptx::tma_store_wait<0>();
   } else {
     // =========================== compute warps ============================================
     ptx::setmaxnreg_inc<kComputeRegs>();
     const int w = warp >> 2;                           // which 64 query columns
     const int n = (warp & 3) * 32 + lane;              // key row inside the tile == TMEM lane
-    const int n_abs = j * kT + n;
-    const bool kv_valid = n_abs < sk;
-    const bool ragged_k = j * kT + kT > sk;            // this CTA's key tile runs past the sequence end
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const float c2 = a.scale_log2;
     uint32_t add7 = 0;
@@ -468,6 +610,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // half-warp share the key block, so each lane draws the 16 bytes of ONE query row per 16-row block
     // (four calls) and the rows are exchanged.  The draws do not depend on S^T: iteration it + 1's four
     // calls are stepped under iteration it's exponentials (five rounds per 8 MUFU, as in the forward).
+    FA_TRACE_DECL(trc, 2 + w, tr_cta && (warp & 3) == 0 && lane == 0);
+    int g0 = 0;
+    for (int item_n = 0;; ++item_n) {
+    const int L = next_item(item_n);
+    if (L < 0) break;
+    const Item I = decode(L);
+    FA_ITEM_LOCALS(I);
+    const int n_abs = j * kT + n;
+    const bool kv_valid = n_abs < sk;
+    const bool ragged_k = j * kT + kT > sk;            // this item's key tile runs past the sequence end
     uint32_t pc[4][4];
     auto ctr_init = [&](int it_) {
       const int hq_ = hk * group + it_ / n_i, i_ = q_tile_of(it_);
@@ -488,10 +640,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
     }
 
-    FA_TRACE_DECL(trc, 2 + w, tr_cta && (warp & 3) == 0 && lane == 0);
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
-      const int s = it & 1;
+      const int g = g0 + it, s = g & 1;
       FA_TRACE_EV(trc, 10);
       const uint32_t stat = sbase + C::kStat + s * 1024 + w * 256;   // lse2 / D of my 64 query columns
       const int q_base = i * kT + w * 64;
@@ -522,9 +673,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         keep_hi = w23;
       }
 
-      ptx::mbar_wait(B.q_full + 8 * s, (it >> 1) & 1);   // LSE / D staged
+      ptx::mbar_wait(B.q_full + 8 * s, (g >> 1) & 1);    // LSE / D staged
       FA_TRACE_EV(trc, 11);
-      ptx::mbar_wait(B.s_full, it & 1);
+      ptx::mbar_wait(B.s_full, g & 1);
       ptx::tc_fence_after();
       FA_TRACE_EV(trc, 12);
       float p[64];
@@ -613,13 +764,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::mbar_arrive(B.p_ready);
       FA_TRACE_EV(trc, 13);
 
-      ptx::mbar_wait(B.dp_full, it & 1);
+      ptx::mbar_wait(B.dp_full, g & 1);
       ptx::tc_fence_after();
       FA_TRACE_EV(trc, 14);
       // GEMMs (5),(4) of it-1 have read dS^T: q_empty is committed after the later of the two (dK).  Long
       // done by now, so waiting here (not after the math) costs nothing and lets each 16-column chunk of
       // dS^T leave for shared memory as soon as it is computed.
-      if (it > 0) ptx::mbar_wait(B.q_empty + 8 * ((it - 1) & 1), ((it - 1) >> 1) & 1);
+      if (g > 0) ptx::mbar_wait(B.q_empty + 8 * ((g - 1) & 1), ((g - 1) >> 1) & 1);
       FA_TRACE_EV(trc, 16);
       {
         // dP^T comes in four 16-column chunks; chunk q + 1 is in flight while chunk q is worked on
@@ -662,60 +813,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       FA_TRACE_EV(trc, 17);
     }
 
-    // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
-    ptx::mbar_wait(B.acc_done, 0);
-    ptx::tc_fence_after();
-    FA_TRACE_EV(trc, 19);
-    // Each thread owns half a ROW of dK / dV; writing it out directly costs one 16-byte store per lane and
-    // row (32 rows, 32 cache lines per instruction: ~8600 cycles per CTA, traced).  Stage both tiles in the
-    // idle Q ring instead (16-byte chunks XOR-swizzled by row) and let all 256 threads write whole rows.
-    constexpr int kHalf = D / 2;                         // columns per warp half
-    constexpr int kRowChunks = D / 8;                    // 16-byte chunks per row
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      const uint32_t tsrc = (which ? tDK : tDV) + lane_sel + w * kHalf;
-      const float mul = n_it == 0 ? 0.f : (which ? a.scale : a.rp_dropout);
-      const uint32_t rowp = sbase + C::kQ + which * C::kTile + n * (D * 2);
-#pragma unroll
-      for (int c = 0; c < kHalf / 32; ++c) {
-        uint32_t v[32];
-        if (n_it > 0) {
-          ptx::tmem_ld_x32(tsrc + c * 32, v);
-          ptx::tmem_wait_ld();
-        } else {
-#pragma unroll
-          for (int x = 0; x < 32; ++x) v[x] = 0;
-        }
-#pragma unroll
-        for (int x = 0; x < 4; ++x) {
-          const int chunk = (w * kHalf + c * 32) / 8 + x;
-          st_shared_v4(rowp + ((chunk ^ (n & 7)) << 4),
-                       pack2(__uint_as_float(v[8 * x]) * mul, __uint_as_float(v[8 * x + 1]) * mul, kBF16),
-                       pack2(__uint_as_float(v[8 * x + 2]) * mul, __uint_as_float(v[8 * x + 3]) * mul, kBF16),
-                       pack2(__uint_as_float(v[8 * x + 4]) * mul, __uint_as_float(v[8 * x + 5]) * mul, kBF16),
-                       pack2(__uint_as_float(v[8 * x + 6]) * mul, __uint_as_float(v[8 * x + 7]) * mul, kBF16));
-        }
-      }
-    }
-    FA_TRACE_EV(trc, 34);
-    ptx::named_bar_sync(2, 256);                         // the eight compute warps
-    FA_TRACE_EV(trc, 35);
-    const int rows_valid = min(kT, sk - j * kT);
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      uint16_t *gbase = static_cast<uint16_t *>(which ? a.dk : a.dv) + ((ktok0 + (size_t)j * kT) * a.hk + hk) * a.d;
-      const uint32_t tile = sbase + C::kQ + which * C::kTile;
-#pragma unroll
-      for (int idx = threadIdx.x; idx < kT * kRowChunks; idx += 256) {
-        const int r = idx / kRowChunks, ch = idx % kRowChunks;
-        uint4 o;
-        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
-                     : "r"(tile + r * (D * 2) + ((ch ^ (r & 7)) << 4)));
-        if (r < rows_valid && ch * 8 < a.d)
-          *reinterpret_cast<uint4 *>(gbase + (size_t)r * a.hk * a.d + ch * 8) = o;
-      }
-    }
+    // (dK_j / dV_j are written out by the drain warps, see above: the compute warps go straight to the next item)
     FA_TRACE_EV(trc, 18);
+    g0 += n_it;
+    }   // items
   }
 
   // ---- teardown -------------------------------------------------------------------------------
@@ -774,6 +875,9 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   if ((e = make_tmap_rows(&tdo, p.dout, kBF16, p.d, p.h, p.sq, nb, kT))) return e;
   if ((e = make_tmap_rows(&tk, p.k, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
   if ((e = make_tmap_rows(&tv, p.v, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+  CUtensorMap tdk, tdv;      // the dK / dV tiles leave through bulk tensor stores
+  if ((e = make_tmap_rows(&tdk, p.dk, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+  if ((e = make_tmap_rows(&tdv, p.dv, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
 
   BwdArgs a;
   a.dk = p.dk; a.dv = p.dv; a.dq_accum = p.dq_accum; a.lse = p.lse; a.softmax_d = p.softmax_d;
@@ -810,10 +914,29 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
       return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
     attr_set = true;
   }
-  dim3 grid((p.sk + kT - 1) / kT, p.hk, p.b);
-  kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, a);
+  a.nkt = (p.sk + kT - 1) / kT;
+  a.n_items = a.nkt * p.hk * p.b;
+  a.persistent = (!p.cu_q && !kOrdered) ? 1 : 0;   // packed: per-CTA tensor maps; ordered dQ: turns assume CTA j starts after 0..j-1
+  a.sched = nullptr;
+  int grid = a.n_items;
+  if (a.persistent) {
+    static int sm_count = 0;
+    if (!sm_count) {
+      int dev = 0;
+      if (cudaGetDevice(&dev) != cudaSuccess ||
+          cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+        return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
+    }
+    grid = a.n_items < sm_count ? a.n_items : sm_count;
+    // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
+    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
+      return "cudaMallocAsync(item counter) failed";
+    if (cudaMemsetAsync(a.sched, 0, sizeof(int), stream) != cudaSuccess) return "cudaMemsetAsync(item counter) failed";
+  }
+  kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, tdk, tdv, a);
   cudaError_t err = cudaGetLastError();
   if (a.sem) cudaFreeAsync(a.sem, stream);
+  if (a.sched) cudaFreeAsync(a.sched, stream);
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
   dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale, a.d,
