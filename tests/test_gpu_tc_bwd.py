@@ -35,6 +35,11 @@ CASES = {
     "d104_dropout": lambda: cases.dense(1, 384, 384, 2, 1, 104, p_dropout=0.1, seed=5, offset=0),
     "d8_tiny": lambda: cases.dense(1, 130, 130, 1, 1, 8, is_causal=True),
     "c2_small_b2h4s2048d128": lambda: cases.dense(2, 2048, 2048, 4, 4, 128, is_causal=True, p_dropout=0.1, seed=5),
+    # persistent CTAs: 640 key-tile items on 148 SMs (4-5 items per CTA: both item-queue slots reused, ring
+    # phases carried across items of different lengths), and a GQA mix with 9 key tiles per sequence
+    "many_items_b10h8s1024d64": lambda: cases.dense(10, 1024, 1024, 8, 8, 64, is_causal=True, p_dropout=0.1, seed=3),
+    "many_items_gqa_s1152d128": lambda: cases.dense(6, 1152, 1152, 16, 4, 128, is_causal=True, p_dropout=0.2, seed=8, offset=5),
+    "many_items_ragged_full": lambda: cases.dense(40, 200, 333, 4, 4, 128),
 }
 
 

@@ -48,6 +48,11 @@ CASES = {
     "d256_packed": lambda: cases.varlen([200, 77, 300], [200, 77, 300], 4, 2, 256, is_causal=True),
     "d200_packed_sq_ne_sk": lambda: cases.varlen([100, 300], [260, 128], 2, 2, 200),
     "c2_small_b2h4s2048d128": lambda: cases.dense(2, 2048, 2048, 4, 4, 128, is_causal=True),
+    # persistent CTAs: 512 / 640 work items on 148 SMs (both item-queue slots reused, O tiles handed from one
+    # item's epilogue to the next item's first P V), with the staged (no dropout) and direct (dropout) epilogues
+    "many_items_b16h8s1024d64": lambda: cases.dense(16, 1024, 1024, 8, 8, 64, is_causal=True),
+    "many_items_dropout_d128": lambda: cases.dense(10, 700, 700, 16, 4, 128, is_causal=True, p_dropout=0.1, seed=21),
+    "many_items_ragged_d72": lambda: cases.dense(40, 300, 450, 4, 2, 72),
 }
 
 
