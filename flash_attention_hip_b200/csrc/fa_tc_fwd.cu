@@ -161,6 +161,9 @@ struct TcFwdArgs {
   int nqb, n_items;      // query blocks per (batch, head); work items = nqb * h * b
   int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
   int *sched;            // global item counter (stream-ordered temporary, zeroed before the launch)
+  // O addressing of the staged epilogue, in elements: out + batch * o_batch + row * o_row + head * o_head
+  // (dense default: sq*h*d, h*d, d; the GQA-packed decode view swaps the roles of heads and rows)
+  long long o_batch, o_row, o_head;
 };
 
 // One unit of work: 256 (128 when D = 256) query rows of one (batch, head).
@@ -660,10 +663,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // rows in its own 4 KB of shared memory (16-byte chunks XOR-swizzled by row) and writes them back
       // as whole 128-byte lines, four rows per instruction.
       const uint32_t stage = sbase + C::kSmemO + (uint32_t)(t * 4 + (warp & 3)) * 4096u;
-      const size_t tok0 = (size_t)(a.cu_q ? q0 : bidx * a.sq) + tile_row0 + (warp & 3) * 32;   // the warp's first row
-      uint16_t *wbase = static_cast<uint16_t *>(a.out) + (tok0 * a.h + head) * a.d;
+      const int wrow0 = tile_row0 + (warp & 3) * 32;                                           // the warp's first row
+      uint16_t *wbase = static_cast<uint16_t *>(a.out) + (a.cu_q ? (size_t)q0 * a.o_row : (size_t)bidx * a.o_batch) +
+                        (size_t)wrow0 * a.o_row + (size_t)head * a.o_head;
       const int rows_left = sq - (tile_row0 + (warp & 3) * 32);                                // rows of this warp inside the sequence
-      const size_t row_pitch = (size_t)a.h * a.d;
+      const size_t row_pitch = (size_t)a.o_row;
       if (n_t > 0) {
         ptx::mbar_wait(B.pv_done + 8 * t, (cnt + n_t - 1) & 1);
         ptx::tc_fence_after();
@@ -794,13 +798,27 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   const uint64_t rows_q = (uint64_t)p.sq, rows_k = (uint64_t)p.sk;
   const uint64_t nb = packed ? 1 : (uint64_t)p.b;
   const char *e;
-  if ((e = make_tmap_rows(&tq, p.q, kBF16, p.d, p.h, rows_q, nb, kTileM))) return e;
+  // Decode-like calls (one query row, GQA, no dropout / bias): the query heads of a K/V head's group become
+  // the ROWS of one tile -- Q [b, 1, h, d] read as [b, group, hk, d] through a strided tensor map -- so a
+  // group streams its K/V head once instead of once per query head.  LSE [b, h, 1] is the same memory
+  // under either view; O goes out through the staged epilogue's strides.  With sq == 1 the (bottom-right
+  // aligned) causal mask hides nothing, so the packed problem is never causal.
+  const int group = p.hk > 0 ? p.h / p.hk : 1;
+  const bool gqa_pack = !packed && p.sq == 1 && group > 1 && p.h % p.hk == 0 && !kDropout && !kMask;
+  const int sq_eff = gqa_pack ? group : p.sq, h_eff = gqa_pack ? p.hk : p.h;
+  if (gqa_pack) {
+    if ((e = make_tmap_strided(&tq, p.q, kBF16, p.d, (uint64_t)p.hk, (uint64_t)group, (uint64_t)p.b,
+                               (uint64_t)group * p.d, (uint64_t)p.d, (uint64_t)p.h * p.d, kTileM))) return e;
+  } else if ((e = make_tmap_rows(&tq, p.q, kBF16, p.d, p.h, rows_q, nb, kTileM))) return e;
   if ((e = make_tmap_rows(&tk, p.k, kBF16, p.d, p.hk, rows_k, nb, kTileN))) return e;
   if ((e = make_tmap_rows(&tv, p.v, kBF16, p.d, p.hk, rows_k, nb, kTileN))) return e;
 
   TcFwdArgs a;
   a.out = p.out; a.lse = p.lse; a.cu_q = p.cu_q; a.cu_k = p.cu_k;
-  a.b = p.b; a.sq = p.sq; a.sk = p.sk; a.h = p.h; a.hk = p.hk; a.batch_base = p.batch_base;
+  a.b = p.b; a.sq = sq_eff; a.sk = p.sk; a.h = h_eff; a.hk = p.hk; a.batch_base = p.batch_base;
+  a.o_batch = gqa_pack ? (long long)p.h * p.d : (long long)p.sq * p.h * p.d;
+  a.o_row = gqa_pack ? (long long)p.d : (long long)p.h * p.d;
+  a.o_head = gqa_pack ? (long long)group * p.d : (long long)p.d;
   a.d = p.d;
   a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
   a.scale_log2 = p.scale * kLog2e;
@@ -809,7 +827,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
   a.key1 = (uint32_t)(p.seed >> 32);
   a.ctr3 = (uint32_t)p.offset;
-  a.causal = p.causal ? 1 : 0;
+  a.causal = (p.causal && !gqa_pack) ? 1 : 0;
 
   auto kern = tc_fwd_kernel<D, kBF16, kDropout, kMask>;
   static bool attr_set = false;   // per instantiation
@@ -818,8 +836,8 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
       return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
     attr_set = true;
   }
-  a.nqb = (p.sq + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
-  a.n_items = a.nqb * p.h * p.b;
+  a.nqb = (sq_eff + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
+  a.n_items = a.nqb * h_eff * p.b;
   a.persistent = packed ? 0 : 1;
   a.sched = nullptr;
   int grid = a.n_items;

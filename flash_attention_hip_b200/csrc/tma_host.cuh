@@ -47,4 +47,23 @@ inline const char *make_tmap_rows(CUtensorMap *m, const void *base, bool is_bf16
   return r == CUDA_SUCCESS ? nullptr : "cuTensorMapEncodeTiled failed";
 }
 
+// The same 4-D view (d, heads, rows, batches) with explicit element strides for heads, rows and batches
+// (each a multiple of 8 elements): lets a caller-side layout be read under another index order, e.g. the
+// query heads of one GQA group as the ROWS of a tile (fa_tc_fwd.cu, decode-like calls).
+inline const char *make_tmap_strided(CUtensorMap *m, const void *base, bool is_bf16, int d, uint64_t heads,
+                                     uint64_t rows, uint64_t batches, uint64_t head_stride, uint64_t row_stride,
+                                     uint64_t batch_stride, int box_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return "cuTensorMapEncodeTiled is unavailable (driver too old?)";
+  const cuuint64_t dims[4] = {(cuuint64_t)d, heads ? heads : 1, rows ? rows : 1, batches ? batches : 1};
+  const cuuint64_t strides[3] = {head_stride * 2, row_stride * 2, batch_stride * 2};
+  const cuuint32_t box[4] = {64, 1, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                         const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? nullptr : "cuTensorMapEncodeTiled failed";
+}
+
 }  // namespace fa

@@ -53,6 +53,12 @@ CASES = {
     "many_items_b16h8s1024d64": lambda: cases.dense(16, 1024, 1024, 8, 8, 64, is_causal=True),
     "many_items_dropout_d128": lambda: cases.dense(10, 700, 700, 16, 4, 128, is_causal=True, p_dropout=0.1, seed=21),
     "many_items_ragged_d72": lambda: cases.dense(40, 300, 450, 4, 2, 72),
+    # decode-like: one query row, GQA -> the group's query heads ride one tile as rows (strided Q map)
+    "decode_gqa_8to2_d128": lambda: cases.dense(3, 1, 700, 8, 2, 128),
+    "decode_gqa_32to8_d128_causal": lambda: cases.dense(5, 1, 1024, 32, 8, 128, is_causal=True),
+    "decode_gqa_12to4_d64_fp16": lambda: cases.dense(2, 1, 333, 12, 4, 64, is_bf16=False),
+    "decode_mqa_16to1_d96": lambda: cases.dense(2, 1, 450, 16, 1, 96),
+    "decode_mha_no_pack": lambda: cases.dense(2, 1, 450, 4, 4, 128),
 }
 
 
