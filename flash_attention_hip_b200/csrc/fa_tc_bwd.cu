@@ -916,18 +916,19 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   }
   a.nkt = (p.sk + kT - 1) / kT;
   a.n_items = a.nkt * p.hk * p.b;
-  a.persistent = (!p.cu_q && !kOrdered) ? 1 : 0;   // packed: per-CTA tensor maps; ordered dQ: turns assume CTA j starts after 0..j-1
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+      return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
+  }
+  // packed: per-CTA tensor maps; ordered dQ: turns assume CTA j starts after 0..j-1; no more items than SMs: no counter needed
+  a.persistent = (!p.cu_q && !kOrdered && a.n_items > sm_count) ? 1 : 0;
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
-    static int sm_count = 0;
-    if (!sm_count) {
-      int dev = 0;
-      if (cudaGetDevice(&dev) != cudaSuccess ||
-          cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-        return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
-    }
-    grid = a.n_items < sm_count ? a.n_items : sm_count;
+    grid = sm_count;
     // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
     if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
       return "cudaMallocAsync(item counter) failed";

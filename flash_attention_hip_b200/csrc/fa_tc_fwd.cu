@@ -97,7 +97,7 @@ constexpr bool stage_o(bool dropout) {
 }
 
 // Per-SM homes of the tensor maps a CTA bounds to its own sequence (packed inputs only).
-__device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][3];
+__device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][2][3];   // two sets: the next sequence's maps are built while the previous ones are in use
 
 struct Bars {
   uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_lo, p_hi, pv_done;  // first of each group
@@ -188,10 +188,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 
   // ---- work items ------------------------------------------------------------
   // Linear order: query blocks fastest inside a (batch, head), heaviest (last) causal block first, so
-  // the CTAs running at any moment share a handful of heads' K/V in L2.  Dense inputs: one CTA per SM
-  // takes items from a global counter (a.sched) until they run out, and its TMA and MMA warps run
-  // ahead into the next item while the softmax warps finish the current one.  Packed inputs: one
-  // item per CTA (the tensor maps are bounded to ONE sequence per CTA, see patch_rows).
+  // the CTAs running at any moment share a handful of heads' K/V in L2.  With more items than SMs one
+  // CTA per SM takes items from a global counter (a.sched) until they run out, and its TMA and MMA warps
+  // run ahead into the next item while the softmax warps finish the current one.  Packed inputs: the
+  // load warp re-bounds its tensor maps whenever the next item belongs to another sequence (patch_rows).
   auto decode = [&](int L) {
     Item it;
     const int hb = L / a.nqb, r = L % a.nqb;
@@ -291,55 +291,75 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   if (warp >= 8) {
     // ======================= producer warpgroup ================================
     ptx::setmaxnreg_dec<40>();
-    const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v;
-    if (warp == kLoadWarp && a.cu_q) {
-      // packed inputs: rows past this sequence's end must read as zero, not as the next sequence
-      const Item it = decode((int)blockIdx.x);
-      const uint32_t sm = ptx::smid();
-      if (sm >= (uint32_t)ptx::kMaxSm) __trap();
-      const uint32_t d0 = sbase + C::kSmemDesc;
-      uint8_t *g0 = sgen + C::kSmemDesc;
-      mq = ptx::patch_rows(tmap_q, &g_fwd_slots[sm][0], d0, g0, (uint32_t)(it.q0 + it.sq), lane);
-      mk = ptx::patch_rows(tmap_k, &g_fwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(it.k0 + it.sk), lane);
-      mv = ptx::patch_rows(tmap_v, &g_fwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(it.k0 + it.sk), lane);
-    }
-    if (warp == kLoadWarp && ptx::elect_one()) {
-      // ---- scheduler + TMA producer ----------------------------------------------
+    if (warp == kLoadWarp) {
+      // ---- scheduler + TMA producer (lane 0 issues; the whole warp builds tensor maps) ----------
+      const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v;
+      int mapped_b = -1, set = 0;   // packed inputs: the sequence the current maps are bounded to
       int nq = 0;        // items that loaded Q so far (q_full / q_empty phases)
       int g = 0;         // KV tiles loaded so far (ring stage and phase)
       for (int n = 0;; ++n) {
-        const int slot = n & 1;
-        if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
-        int L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
-        if (L >= a.n_items) L = -1;
-        sched_item[slot] = L;
-        ptx::mbar_arrive(B.sched_full + 8 * slot);
+        int L = 0;
+        if (lane == 0) {
+          const int slot = n & 1;
+          if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
+          L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
+          if (L >= a.n_items) L = -1;
+          sched_item[slot] = L;
+          ptx::mbar_arrive(B.sched_full + 8 * slot);
+        }
+        L = __shfl_sync(0xffffffffu, L, 0);
         if (L < 0) break;
         const Item it = decode(L);
         if (!it.valid || it.nmax == 0) continue;
-        const int qrow = it.q0 * (a.cu_q ? 1 : 0) + it.m0;   // packed: absolute token row; dense: row in sequence
-        const int krow = it.k0 * (a.cu_q ? 1 : 0);
-        if (nq >= 1) ptx::mbar_wait(B.q_empty, (nq - 1) & 1);  // the previous item's S = Q K^T are all done
-        ++nq;
-        ptx::mbar_arrive_expect_tx(B.q_full, (it.has_tile1 ? 2 : 1) * C::kTileBytes);
-        for (int t = 0; t < (it.has_tile1 ? 2 : 1); ++t)
-          for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, mq, B.q_full,
-                             c * 64, it.head, qrow + t * kTileM, it.bcoord);
-        for (int j = 0; j < it.nmax; ++j, ++g) {
-          const int s = g % C::kStages;
-          const uint32_t ph = (g / C::kStages) & 1;
-          if (g >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
-          ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
-          for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, mk,
-                             B.k_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
-          if (g >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
-          ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
-          for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, mv,
-                             B.v_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
+        if (a.cu_q && it.bidx != mapped_b) {
+          // packed inputs: rows past this sequence's end must read as zero, not as the next sequence.  Loads in
+          // flight may still be reading the maps of the previous sequence: two sets of per-SM slots alternate, and
+          // (a change of sequence is rare) every load issued so far is seen complete before a set is rewritten.
+          if (lane == 0 && mapped_b >= 0) {
+            if (nq >= 1) ptx::mbar_wait(B.q_full, (nq - 1) & 1);
+            for (int t = max(0, g - C::kStages); t < g; ++t) {
+              ptx::mbar_wait(B.k_full + 8 * (t % C::kStages), (t / C::kStages) & 1);
+              ptx::mbar_wait(B.v_full + 8 * (t % C::kStages), (t / C::kStages) & 1);
+            }
+          }
+          __syncwarp();
+          const uint32_t sm = ptx::smid();
+          if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+          const uint32_t d0 = sbase + C::kSmemDesc;
+          uint8_t *g0 = sgen + C::kSmemDesc;
+          mq = ptx::patch_rows(tmap_q, &g_fwd_slots[sm][set][0], d0, g0, (uint32_t)(it.q0 + it.sq), lane);
+          mk = ptx::patch_rows(tmap_k, &g_fwd_slots[sm][set][1], d0 + 128, g0 + 128, (uint32_t)(it.k0 + it.sk), lane);
+          mv = ptx::patch_rows(tmap_v, &g_fwd_slots[sm][set][2], d0 + 256, g0 + 256, (uint32_t)(it.k0 + it.sk), lane);
+          mapped_b = it.bidx;
+          set ^= 1;
         }
+        if (lane == 0) {
+          const int qrow = it.q0 * (a.cu_q ? 1 : 0) + it.m0;   // packed: absolute token row; dense: row in sequence
+          const int krow = it.k0 * (a.cu_q ? 1 : 0);
+          if (nq >= 1) ptx::mbar_wait(B.q_empty, (nq - 1) & 1);  // the previous item's S = Q K^T are all done
+          ptx::mbar_arrive_expect_tx(B.q_full, (it.has_tile1 ? 2 : 1) * C::kTileBytes);
+          for (int t = 0; t < (it.has_tile1 ? 2 : 1); ++t)
+            for (int c = 0; c < D / 64; ++c)
+              ptx::tma_load_4d(sbase + C::kSmemQ + t * C::kTileBytes + c * C::kSubBytes, mq, B.q_full,
+                               c * 64, it.head, qrow + t * kTileM, it.bcoord);
+          int gg = g;
+          for (int j = 0; j < it.nmax; ++j, ++gg) {
+            const int s = gg % C::kStages;
+            const uint32_t ph = (gg / C::kStages) & 1;
+            if (gg >= C::kStages) ptx::mbar_wait(B.k_empty + 8 * s, ph ^ 1);
+            ptx::mbar_arrive_expect_tx(B.k_full + 8 * s, C::kTileBytes);
+            for (int c = 0; c < D / 64; ++c)
+              ptx::tma_load_4d(sbase + C::kSmemK + s * C::kTileBytes + c * C::kSubBytes, mk,
+                               B.k_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
+            if (gg >= C::kStages) ptx::mbar_wait(B.v_empty + 8 * s, ph ^ 1);
+            ptx::mbar_arrive_expect_tx(B.v_full + 8 * s, C::kTileBytes);
+            for (int c = 0; c < D / 64; ++c)
+              ptx::tma_load_4d(sbase + C::kSmemV + s * C::kTileBytes + c * C::kSubBytes, mv,
+                               B.v_full + 8 * s, c * 64, it.hk, krow + j * kTileN, it.bcoord);
+          }
+        }
+        ++nq;
+        g += it.nmax;
       }
     } else if (warp == kMmaWarp && ptx::elect_one()) {
       // ---- MMA issuer ------------------------------------------------------------
@@ -838,18 +858,19 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   }
   a.nqb = (sq_eff + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
   a.n_items = a.nqb * h_eff * p.b;
-  a.persistent = packed ? 0 : 1;
+  static int sm_count = 0;
+  if (!sm_count) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
+      return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
+  }
+  // no more items than SMs: one item per CTA needs no counter (and no allocation / memset on a latency-bound call)
+  a.persistent = a.n_items > sm_count ? 1 : 0;
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
-    static int sm_count = 0;
-    if (!sm_count) {
-      int dev = 0;
-      if (cudaGetDevice(&dev) != cudaSuccess ||
-          cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-        return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
-    }
-    grid = a.n_items < sm_count ? a.n_items : sm_count;
+    grid = sm_count;
     // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
     if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
       return "cudaMallocAsync(item counter) failed";
