@@ -65,7 +65,7 @@ struct Cfg {
   static_assert(kBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
 
-__device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][6];
+__device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][2][6];   // two alternating sets (packed inputs)
 
 struct BwdArgs {
   void *dk, *dv;
@@ -288,19 +288,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (warp == kLoadWarp) {
       // ---- TMA producer; all 32 lanes stage LSE / D -----------------------------------------
       const CUtensorMap *mq = &tmap_q, *mk = &tmap_k, *mv = &tmap_v, *mdo = &tmap_do;
-      if (a.cu_q) {
-        // packed inputs (one item per CTA): rows past this sequence's end must read as zero, not as the next sequence
-        const Item I0 = decode((int)blockIdx.x);
-        const int qrow0 = I0.qrow0, krow0 = I0.krow0, sq = I0.sq, sk = I0.sk;
-        const uint32_t sm = ptx::smid();
-        if (sm >= (uint32_t)ptx::kMaxSm) __trap();
-        const uint32_t d0 = sbase + C::kDesc;
-        uint8_t *g0 = smem_raw + C::kDesc;
-        mq = ptx::patch_rows(tmap_q, &g_bwd_slots[sm][0], d0, g0, (uint32_t)(qrow0 + sq), lane);
-        mdo = ptx::patch_rows(tmap_do, &g_bwd_slots[sm][1], d0 + 128, g0 + 128, (uint32_t)(qrow0 + sq), lane);
-        mk = ptx::patch_rows(tmap_k, &g_bwd_slots[sm][2], d0 + 256, g0 + 256, (uint32_t)(krow0 + sk), lane);
-        mv = ptx::patch_rows(tmap_v, &g_bwd_slots[sm][3], d0 + 384, g0 + 384, (uint32_t)(krow0 + sk), lane);
-      }
+      int mapped_b = -1, set = 0, nv = 0;              // packed: sequence the maps are bounded to; valid items so far
       int g0 = 0;                                      // iterations of the items before this one (ring stages, phases)
       for (int n = 0;; ++n) {
       // ---- scheduler: lane 0 takes the next item and publishes it to the other roles ----
@@ -316,8 +304,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       L = __shfl_sync(0xffffffffu, L, 0);
       if (L < 0) break;
       const Item I = decode(L);
+      if (!I.valid) continue;                          // packed: this sequence has no such key tile
       FA_ITEM_LOCALS(I);
-      if (n >= 1) ptx::mbar_wait(B.acc_done, (n - 1) & 1);   // the previous item's MMAs have read K and V
+      if (nv >= 1) ptx::mbar_wait(B.acc_done, (nv - 1) & 1);   // the previous item's MMAs have read K and V
+      if (a.cu_q && bidx != mapped_b) {
+        // packed inputs: rows past this sequence's end must read as zero, not as the next sequence.  Every load
+        // issued so far has been consumed (acc_done above), so the other slot set may be rewritten.
+        const uint32_t sm = ptx::smid();
+        if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+        const uint32_t d0 = sbase + C::kDesc;
+        uint8_t *gen0 = smem_raw + C::kDesc;
+        mq = ptx::patch_rows(tmap_q, &g_bwd_slots[sm][set][0], d0, gen0, (uint32_t)(qrow0 + sq), lane);
+        mdo = ptx::patch_rows(tmap_do, &g_bwd_slots[sm][set][1], d0 + 128, gen0 + 128, (uint32_t)(qrow0 + sq), lane);
+        mk = ptx::patch_rows(tmap_k, &g_bwd_slots[sm][set][2], d0 + 256, gen0 + 256, (uint32_t)(krow0 + sk), lane);
+        mv = ptx::patch_rows(tmap_v, &g_bwd_slots[sm][set][3], d0 + 384, gen0 + 384, (uint32_t)(krow0 + sk), lane);
+        mapped_b = bidx;
+        set ^= 1;
+      }
       if (lane == 0) {
         ptx::mbar_arrive_expect_tx(B.kv_full, 2 * C::kTile);
         for (int c = 0; c < D / 64; ++c) {
@@ -359,6 +362,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
       g0 += n_it;
+      ++nv;
       }   // items
     } else if (warp == kMmaWarp && ptx::elect_one()) {
       // ---- MMA issuer -----------------------------------------------------------------------
@@ -378,13 +382,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       };
       FA_TRACE_DECL(tr, 0, tr_cta);
-      int g0 = 0;
+      int g0 = 0, nv = 0;
       for (int n = 0;; ++n) {
       const int L = next_item(n);
       if (L < 0) break;
       const Item I = decode(L);
+      if (!I.valid) continue;
       FA_ITEM_LOCALS(I);
-      ptx::mbar_wait(B.kv_full, n & 1);
+      ptx::mbar_wait(B.kv_full, nv & 1);
       ptx::tc_fence_after();
       if (n_it > 0) {
         ptx::mbar_wait(B.q_full + 8 * (g0 & 1), (g0 >> 1) & 1);
@@ -407,7 +412,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::mma_commit(B.dp_full);
         ptx::mbar_wait(B.p_ready, g & 1);
         // the first dV / dK MMAs of an item overwrite the accumulators: the previous item's epilogue must have read them
-        if (it == 0 && n >= 1) ptx::mbar_wait(B.epi_tmem_free, (n - 1) & 1);
+        if (it == 0 && nv >= 1) ptx::mbar_wait(B.epi_tmem_free, (nv - 1) & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 4);
 #pragma unroll
@@ -442,6 +447,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       ptx::mma_commit(B.acc_done);
       g0 += n_it;
+      ++nv;
       }   // items
     }
   } else if (warp >= kDrainWarp0) {
@@ -456,24 +462,28 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const bool leader = (warp == kDrainWarp0 && lane == 0);
     uint32_t cc = 0;                                   // running 16 KB block counter (staging ring of 2)
     const CUtensorMap *mdk = &tmap_dk, *mdv = &tmap_dv;
-    if (a.cu_q && warp == kDrainWarp0) {
-      // packed inputs (one item per CTA): rows past this sequence's end belong to the next sequence -- clip the stores
-      const Item I0 = decode((int)blockIdx.x);
-      const uint32_t sm = ptx::smid();
-      if (sm >= (uint32_t)ptx::kMaxSm) __trap();
-      const uint32_t d0 = sbase + C::kDesc;
-      uint8_t *gen0 = smem_raw + C::kDesc;
-      mdk = ptx::patch_rows(tmap_dk, &g_bwd_slots[sm][4], d0 + 512, gen0 + 512, (uint32_t)(I0.krow0 + I0.sk), lane);
-      mdv = ptx::patch_rows(tmap_dv, &g_bwd_slots[sm][5], d0 + 640, gen0 + 640, (uint32_t)(I0.krow0 + I0.sk), lane);
-    }
-    if (leader) { ptx::prefetch_tensormap(mdk); ptx::prefetch_tensormap(mdv); }
     FA_TRACE_DECL(trd, 1, tr_cta && leader);
-    int g0 = 0;
+    int g0 = 0, nv = 0, mapped_b = -1, set = 0;
     for (int n = 0;; ++n) {
     const int L = next_item(n);
     if (L < 0) break;
     const Item I = decode(L);
+    if (!I.valid) continue;
     FA_ITEM_LOCALS(I);
+    if (a.cu_q && warp == kDrainWarp0 && bidx != mapped_b) {
+      // packed inputs: rows past this sequence's end belong to the next sequence -- the dK / dV stores are clipped by
+      // maps bounded to this one.  The stores of the previous sequence must be over before its set is rewritten.
+      if (lane == 0) ptx::tma_store_wait<0>();
+      __syncwarp();
+      const uint32_t sm = ptx::smid();
+      if (sm >= (uint32_t)ptx::kMaxSm) __trap();
+      const uint32_t d0 = sbase + C::kDesc;
+      uint8_t *gen0 = smem_raw + C::kDesc;
+      mdk = ptx::patch_rows(tmap_dk, &g_bwd_slots[sm][set][4], d0 + 512, gen0 + 512, (uint32_t)(krow0 + sk), lane);
+      mdv = ptx::patch_rows(tmap_dv, &g_bwd_slots[sm][set][5], d0 + 640, gen0 + 640, (uint32_t)(krow0 + sk), lane);
+      mapped_b = bidx;
+      set ^= 1;
+    }
     for (int it = 0; it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
@@ -546,7 +556,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // are clipped by the map) -- while the compute warps are already in the next item.  (They used to stage
     // both tiles in the Q ring and write them out themselves: ~5000 cycles per item on a store port the dQ
     // tiles keep 64 % busy.  One small bulk copy per row was measured too: ~18 cycles per copy, 18800 per item.)
-    ptx::mbar_wait(B.acc_done, n & 1);
+    ptx::mbar_wait(B.acc_done, nv & 1);
     ptx::tc_fence_after();
     FA_TRACE_EV(trd, 23);
 #pragma unroll
@@ -590,6 +600,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     }
     FA_TRACE_EV(trd, 24);
     g0 += n_it;
+    ++nv;
     }   // items
     if (leader) ptx::tma_store_wait<0>();
   } else {
@@ -616,6 +627,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const int L = next_item(item_n);
     if (L < 0) break;
     const Item I = decode(L);
+    if (!I.valid) continue;
     FA_ITEM_LOCALS(I);
     const int n_abs = j * kT + n;
     const bool kv_valid = n_abs < sk;
@@ -923,8 +935,8 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
         cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
       return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
   }
-  // packed: per-CTA tensor maps; ordered dQ: turns assume CTA j starts after 0..j-1; no more items than SMs: no counter needed
-  a.persistent = (!p.cu_q && !kOrdered && a.n_items > sm_count) ? 1 : 0;
+  // ordered dQ: its turns assume CTA j starts after CTAs 0..j-1; no more items than SMs: no counter needed
+  a.persistent = (!kOrdered && a.n_items > sm_count) ? 1 : 0;
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
