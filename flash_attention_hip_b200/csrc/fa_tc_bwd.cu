@@ -171,7 +171,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
   constexpr bool kEarlyDrain = true;
   // drain / compute registers per thread; 4 x 32 (producers) + 4 x drain + 8 x compute = 2048
-  constexpr int kDrainRegs = D == 64 ? 128 : (kDropout ? FA_BWD_DRAIN_REGS : 208);
+  constexpr int kDrainRegs = D == 64 ? 128 : ((kDropout || kMask) ? FA_BWD_DRAIN_REGS : 208);   // bias: 64 prefetched words
   constexpr int kComputeRegs = (2048 - 128 - 4 * kDrainRegs) / 8;
   static_assert(kComputeRegs % 8 == 0 && kDrainRegs % 8 == 0, "setmaxnreg takes multiples of 8");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -685,6 +685,17 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         keep_hi = w23;
       }
 
+      // attn_mask (reference flash_attn.h:98-99): the 64 bias values of my key and the iteration's query rows do not
+      // depend on S^T either -- fetched before the wait for it, so the loads' latency is spent waiting anyway
+      // (lanes hold consecutive keys: each load instruction reads 64 contiguous bytes of one mask row)
+      uint16_t mbias[kMask ? 64 : 1];
+      if constexpr (kMask) {
+        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
+            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * sq + q_base) * (size_t)sk + n_abs;
+#pragma unroll
+        for (int c = 0; c < 64; ++c)
+          mbias[c] = (kv_valid && q_base + c < sq) ? __ldg(mp + (size_t)c * sk) : (uint16_t)0;
+      }
       ptx::mbar_wait(B.q_full + 8 * s, (g >> 1) & 1);    // LSE / D staged
       FA_TRACE_EV(trc, 11);
       ptx::mbar_wait(B.s_full, g & 1);
@@ -702,17 +713,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
       const int lim = n_abs - shift;                     // causal: visible iff q >= lim
       float cs = c2;
-      if constexpr (kMask) {                                      // uniform: attn_mask (reference flash_attn.h:98-99)
-        // s <- s * scale_log2 + bias * log2 e; lanes hold consecutive keys, so each load is coalesced
-        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
-            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * sq + q_base) * (size_t)sk + n_abs;
+      if constexpr (kMask) {                                      // s <- s * scale_log2 + bias * log2 e
 #pragma unroll
         for (int c = 0; c < 64; ++c) {
-          float bias = 0.f;
-          if (kv_valid && q_base + c < sq) {
-            const uint16_t mb = mp[(size_t)c * sk];
-            bias = kBF16 ? __uint_as_float((uint32_t)mb << 16) : __half2float(*reinterpret_cast<const __half *>(&mb));
-          }
+          const uint16_t mb = mbias[c];
+          const float bias = kBF16 ? __uint_as_float((uint32_t)mb << 16) : __half2float(*reinterpret_cast<const __half *>(&mb));
           p[c] = fmaf(p[c], c2, bias * kLog2e);
         }
         cs = 1.f;
