@@ -179,6 +179,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               const __grid_constant__ CUtensorMap tmap_v, const TcFwdArgs a) {
   using C = Cfg<D>;
   constexpr bool kStageO = stage_o(kDropout);
+  constexpr bool kMaskStage = kMask && kStageO;       // the bias tile borrows the epilogue's staging blocks
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *sgen = smem_raw + (sbase - ptx::smem_u32(smem_raw));
@@ -486,6 +487,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       mrow = static_cast<const uint16_t *>(a.mask) +
              (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * sq + row) * (size_t)sk;
     const bool mvec = (sk % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.mask) & 15) == 0);
+    const uint16_t *mbase = kMask ? static_cast<const uint16_t *>(a.mask) +
+        ((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * (size_t)sq * sk : nullptr;
     const int row_limit = row + shift;                // last visible key when causal
     const int tile_row0 = m0 + t * kTileM;
     uint32_t bh = 0;
@@ -516,6 +519,34 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
     }
     for (int j = 0; j < n_t; ++j) {
+      // attn_mask, whole tiles of 16-byte aligned rows (non-dropout builds, which own a 4 KB staging block per
+      // warp): a lane per ROW would fetch 16 bytes from each of 32 cache lines per instruction.  Instead the warp
+      // reads its 32 rows x 128 columns as whole 128-byte lines (four rows per instruction), before the wait
+      // for S -- the bias does not depend on it -- and turns them into rows through the staging block below.
+      // The first 64 columns are parked in the block right away, the other 64 wait in registers.
+      uint4 mpre[kMaskStage ? 8 : 1];
+      bool mfast = false;
+      if constexpr (kMaskStage) {
+        mfast = mvec && (j * kTileN + kTileN <= sk);
+        if (mfast) {
+          const uint16_t *mtile = mbase + (size_t)(tile_row0 + (warp & 3) * 32) * sk + j * kTileN;
+          const int rows_in = sq - (tile_row0 + (warp & 3) * 32);
+          const uint32_t mstage = sbase + C::kSmemO + (uint32_t)(t * 4 + (warp & 3)) * 4096u;
+          uint4 m0v[8];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int r = (i % 8) * 4 + (lane >> 3);
+            const uint4 v = r < rows_in ? __ldg(reinterpret_cast<const uint4 *>(mtile + (size_t)r * sk + (i / 8) * 64 + (lane & 7) * 8))
+                                        : make_uint4(0, 0, 0, 0);
+            if (i < 8) m0v[i] = v; else mpre[i - 8] = v;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = i * 4 + (lane >> 3), ch = lane & 7;
+            st_shared_v4(mstage + r * 128 + ((ch ^ (r & 7)) << 4), m0v[i].x, m0v[i].y, m0v[i].z, m0v[i].w);
+          }
+        }
+      }
       FA_TRACE_EV(trs, 10);
       ptx::mbar_wait(B.s_full + 8 * t, (cnt + j) & 1);
       ptx::tc_fence_after();
@@ -534,7 +565,35 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
       FA_TRACE_EV(trs, 12);
       const int col0 = j * kTileN;
-      if constexpr (kMask) {                                   // uniform: attn_mask (reference flash_attn.h:35-36)
+      if (kMaskStage && mfast) {                               // uniform: attn_mask through the staging block
+        const float sc = a.scale_log2;
+        const uint32_t mstage = sbase + C::kSmemO + (uint32_t)(t * 4 + (warp & 3)) * 4096u;
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          if (hf == 1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = i * 4 + (lane >> 3), ch = lane & 7;
+              st_shared_v4(mstage + r * 128 + ((ch ^ (r & 7)) << 4), mpre[i].x, mpre[i].y, mpre[i].z, mpre[i].w);
+            }
+          }
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint4 v = ld_shared_v4(mstage + lane * 128 + ((k ^ (lane & 7)) << 4));
+            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const uint16_t mb = (uint16_t)(w4[e / 2] >> (16 * (e & 1)));
+              const float bias = kBF16 ? __uint_as_float((uint32_t)mb << 16)
+                                       : __half2float(*reinterpret_cast<const __half *>(&mb));
+              const int c = hf * 64 + k * 8 + e;
+              s[c] = __float_as_uint(fmaf(__uint_as_float(s[c]), sc, bias * kLog2e));
+            }
+          }
+          __syncwarp();
+        }
+      } else if constexpr (kMask) {                            // uniform: attn_mask (reference flash_attn.h:35-36)
         const float sc = a.scale_log2;
 #pragma unroll
         for (int c8 = 0; c8 < kTileN; c8 += 8) {

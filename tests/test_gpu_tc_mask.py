@@ -30,6 +30,9 @@ CASES = {
     "sk_not_multiple_of_8": (lambda: cases.dense(1, 130, 203, 2, 1, 128, is_causal=True), 1, 2, None, 0),
     "dropout_and_mask": (lambda: cases.dense(1, 384, 384, 2, 2, 128, p_dropout=0.2, seed=9, offset=2), 1, 2, None, 0),
     "d96_mask": (lambda: cases.dense(1, 192, 192, 2, 2, 96, is_causal=True), 1, 1, None, 0),
+    # several KV tiles and items per CTA: the bias tile borrows the epilogue's staging block (forward), prefetch in the backward
+    "many_tiles_bh": (lambda: cases.dense(3, 700, 1024, 4, 2, 128, is_causal=True), 3, 4, None, 0),
+    "many_items_b1h1": (lambda: cases.dense(24, 520, 520, 8, 8, 64), 1, 1, None, 0),
 }
 
 
