@@ -78,6 +78,8 @@ struct BwdArgs {
   int *sem;              // deterministic dQ (num_splits == 1): one turn counter per (batch, head, query tile)
   int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
+  float keep_prob;       // 1 - p_dropout.  dS is computed as P o (keep o dP - D (1 - p)) = (1 - p) dS; the factor 1 / (1 - p)
+                         // rides on the final scales of dQ and dK (one multiply per output element, not per score)
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
   int nkt, n_items;      // key tiles per sequence (dense: of sk; packed: of the longest); items = nkt * hk * b
@@ -349,7 +351,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             const float l = row < sq ? lse[row] : INFINITY;
             const float dv = row < sq ? dd[row] : 0.f;
             asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 4 * r), "f"(-l * kLog2e) : "memory");
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 512 + 4 * r), "f"(-dv) : "memory");
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(st + 512 + 4 * r), "f"(-dv * a.keep_prob) : "memory");
           }
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(B.q_full + 8 * s);
@@ -561,7 +563,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     FA_TRACE_EV(trd, 23);
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
-      const float mul = which ? a.scale : a.rp_dropout;
+      const float mul = which ? a.scale * a.rp_dropout : a.rp_dropout;
 #pragma unroll
       for (int c = 0; c < D / 64; ++c) {
         const uint32_t buf = sbase + C::kDQ + (cc & 1) * 16384;
@@ -806,10 +808,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             float2 g01 = ptx::u2f2(dp[c], dp[c + 1]), g23 = ptx::u2f2(dp[c + 2], dp[c + 3]);
             if constexpr (kDropout) {
               const uint32_t kb = cq < 32 ? keep_lo >> cq : keep_hi >> (cq - 32);
-              g01.x = (kb & 1u) ? g01.x * a.rp_dropout : 0.f;
-              g01.y = (kb & 2u) ? g01.y * a.rp_dropout : 0.f;
-              g23.x = (kb & 4u) ? g23.x * a.rp_dropout : 0.f;
-              g23.y = (kb & 8u) ? g23.y * a.rp_dropout : 0.f;
+              g01.x = (kb & 1u) ? g01.x : 0.f;
+              g01.y = (kb & 2u) ? g01.y : 0.f;
+              g23.x = (kb & 4u) ? g23.x : 0.f;
+              g23.y = (kb & 8u) ? g23.y : 0.f;
             }
             const float4 nd = ld_shared_f32x4(stat + 512 + 4 * cq);        // -D of 4 query columns
             const float2 e01 = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(g01, make_float2(nd.x, nd.y)));
@@ -906,6 +908,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.nblk = (p.d + 31) / 32;
   a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
+  a.keep_prob = kDropout ? 1.f - p.p_dropout : 1.f;
   a.drop_threshold = p.drop_threshold;
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);
   a.key1 = (uint32_t)(p.seed >> 32);
@@ -957,7 +960,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   if (a.sched) cudaFreeAsync(a.sched, stream);
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
-  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale, a.d,
+  dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale * p.rp_dropout, a.d,
                                                          a.nblk);
   err = cudaGetLastError();
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
