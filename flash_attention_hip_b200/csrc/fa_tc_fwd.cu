@@ -164,6 +164,7 @@ struct TcFwdArgs {
   // O addressing of the staged epilogue, in elements: out + batch * o_batch + row * o_row + head * o_head
   // (dense default: sq*h*d, h*d, d; the GQA-packed decode view swaps the roles of heads and rows)
   long long o_batch, o_row, o_head;
+  int use_emu;           // D = 64 builds: FMA-pipe exp2 on (long key sequences) or off (short ones: -8 % at S1024 causal)
 };
 
 // One unit of work: 256 (128 when D = 256) query rows of one (batch, head).
@@ -707,8 +708,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
           for (int q = 0; q < 4; ++q) ctr_init(q, half ? j + 1 : j, 1 - half);
         }
-        if (kEmuPer8 == 0 || need_mask) exp_half(std::integral_constant<int, 0>{}, half);
-        else exp_half(std::integral_constant<int, kEmuPer8>{}, half);
+        // D = 64 without dropout is the most exponential-bound build (half the MMA work per exp2): there 4 of
+        // every 8 exponentials on the FMA pipe pay (635 -> 690 TFLOP/s at S4096 causal, 679 -> 780 without the mask,
+        // varlen mix 480 -> 520-580; host switch a.use_emu: off below 1536 keys); at D = 128 they gain
+        // 4 % at S4096 but lose 2 % at S2048, and with dropout they wreck the draw-ahead schedule (881 -> 629)
+        constexpr int kEmu = (kEmuPer8 == 0 && D == 64 && !kDropout) ? 4 : kEmuPer8;
+        if (kEmu == 0 || need_mask || !a.use_emu) exp_half(std::integral_constant<int, 0>{}, half);
+        else exp_half(std::integral_constant<int, kEmu>{}, half);
         if constexpr (kDropout) {
           if (!kApplyInGroup) {
 #pragma unroll
@@ -907,6 +913,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.key1 = (uint32_t)(p.seed >> 32);
   a.ctr3 = (uint32_t)p.offset;
   a.causal = (p.causal && !gqa_pack) ? 1 : 0;
+  a.use_emu = p.sk >= 1536 ? 1 : 0;
 
   auto kern = tc_fwd_kernel<D, kBF16, kDropout, kMask>;
   static bool attr_set = false;   // per instantiation
