@@ -51,6 +51,10 @@ def lib() -> ctypes.CDLL:
             fn = getattr(l, name)
             fn.argtypes = args
             fn.restype = ctypes.c_bool
+            # batch-shard variants (include/flash_attn_b200_ext.h): the same call with a leading batch_base
+            fn = getattr(l, name.replace("flash_attn_", "flash_attn_b200_") + "_shard")
+            fn.argtypes = [_i] + args
+            fn.restype = ctypes.c_bool
         l.flash_attn_error.restype = ctypes.c_char_p
         l.flash_attn_set_error.argtypes = [ctypes.c_char_p]
         l.flash_attn_b200_version.restype = ctypes.c_char_p
@@ -93,6 +97,13 @@ def _stream_ptr(stream: Optional[torch.cuda.Stream]):
     return ctypes.c_void_p(s.cuda_stream)
 
 
+def _call(name: str, batch_base: int, *args) -> bool:
+    """The reference entry point `name`, or its `_shard` variant when the caller is a batch shard."""
+    if batch_base:
+        return getattr(lib(), name.replace("flash_attn_", "flash_attn_b200_") + "_shard")(int(batch_base), *args)
+    return getattr(lib(), name)(*args)
+
+
 def _mask_args(attn_mask: Optional[torch.Tensor]):
     if attn_mask is None:
         return None, None, None
@@ -105,7 +116,8 @@ def flash_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, p_dropo
                    softmax_scale: Optional[float] = None, is_causal: bool = False,
                    return_softmax: bool = False, seed: int = 0, offset: int = 0,
                    attn_mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
-                   lse: Optional[torch.Tensor] = None, stream: Optional[torch.cuda.Stream] = None):
+                   lse: Optional[torch.Tensor] = None, stream: Optional[torch.cuda.Stream] = None,
+                   batch_base: int = 0):
     """Dense forward.  q [b, sq, h, d]; k, v [b, sk, hk, d]; fp16 or bf16, contiguous.
     Returns (out, softmax_lse [b, h, sq] fp32, softmax or None, rng_state [2] int64)."""
     assert q.is_cuda and q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
@@ -121,10 +133,10 @@ def flash_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, p_dropo
     sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
     rng = torch.empty(2, dtype=torch.int64, device=q.device)
     mptr, mdims, _keep = _mask_args(attn_mask)
-    ok = lib().flash_attn_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse),
-                              b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
-                              1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
-                              q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset, mptr, mdims)
+    ok = _call("flash_attn_fwd", batch_base, _ptr(q), _ptr(k), _ptr(v), _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse),
+               b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+               1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
+               q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset, mptr, mdims)
     _check(ok, "flash_attn_fwd")
     return out, lse, sm, rng
 
@@ -135,7 +147,8 @@ def flash_attn_varlen_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
                           softmax_scale: Optional[float] = None, is_causal: bool = False,
                           return_softmax: bool = False, seed: int = 0, offset: int = 0,
                           out: Optional[torch.Tensor] = None, lse: Optional[torch.Tensor] = None,
-                          stream: Optional[torch.cuda.Stream] = None):
+                          stream: Optional[torch.cuda.Stream] = None, attn_mask: Optional[torch.Tensor] = None,
+                          batch_base: int = 0):
     """Packed forward.  q [total_q, h, d]; k, v [total_k, hk, d]; cu_seqlens int32 [b+1] on device.
     Returns (out, softmax_lse [b, h, max_seqlen_q], softmax or None, rng_state)."""
     assert q.is_cuda and q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
@@ -151,12 +164,12 @@ def flash_attn_varlen_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor,
         lse = torch.full((b, h, max_seqlen_q), float("inf"), dtype=torch.float32, device=q.device)
     sm = torch.zeros((b, h, sq_r, sk_r), dtype=q.dtype, device=q.device) if return_softmax else None
     rng = torch.empty(2, dtype=torch.int64, device=q.device)
-    ok = lib().flash_attn_varlen_fwd(_ptr(q), _ptr(k), _ptr(v), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k),
-                                     _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse), b, max_seqlen_q,
-                                     max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
-                                     1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
-                                     q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset,
-                                     None, None)
+    mptr, mdims, _keep = _mask_args(attn_mask)
+    ok = _call("flash_attn_varlen_fwd", batch_base, _ptr(q), _ptr(k), _ptr(v), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k),
+               _ptr(rng), _ptr(out), _ptr(sm), _ptr(lse), b, max_seqlen_q,
+               max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+               1.0 / scale if scale != 0 else 0.0, is_causal, return_softmax,
+               q.dtype == torch.bfloat16, _stream_ptr(stream), seed, offset, mptr, mdims)
     _check(ok, "flash_attn_varlen_fwd")
     return out, lse, sm, rng
 
@@ -172,8 +185,8 @@ def flash_attn_bwd(dout, q, k, v, out, softmax_lse, *, p_dropout: float = 0.0,
                    deterministic: bool = False, seed: int = 0, offset: int = 0,
                    attn_mask: Optional[torch.Tensor] = None, scratch=None,
                    grads: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
-                   stream: Optional[torch.cuda.Stream] = None):
-    """Dense backward; returns (dq, dk, dv).  seed/offset must be the forward's."""
+                   stream: Optional[torch.cuda.Stream] = None, batch_base: int = 0):
+    """Dense backward; returns (dq, dk, dv).  seed/offset/batch_base must be the forward's."""
     for t in (dout, q, k, v, out):
         assert t.is_cuda and t.is_contiguous()
     b, sq, h, d = q.shape
@@ -183,12 +196,12 @@ def flash_attn_bwd(dout, q, k, v, out, softmax_lse, *, p_dropout: float = 0.0,
     softmax_d, dq_accum = scratch if scratch is not None else _bwd_scratch(b, sq_r, h, d_r, q.device)
     dq, dk, dv = grads if grads is not None else (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
     mptr, mdims, _keep = _mask_args(attn_mask)
-    ok = lib().flash_attn_bwd(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
-                              _ptr(softmax_lse), None, _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum),
-                              b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
-                              1.0 / scale if scale != 0 else 0.0, is_causal,
-                              q.dtype == torch.bfloat16, 1 if deterministic else 0,
-                              _stream_ptr(stream), seed, offset, mptr, mdims)
+    ok = _call("flash_attn_bwd", batch_base, _ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
+               _ptr(softmax_lse), None, _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum),
+               b, sq, sk, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+               1.0 / scale if scale != 0 else 0.0, is_causal,
+               q.dtype == torch.bfloat16, 1 if deterministic else 0,
+               _stream_ptr(stream), seed, offset, mptr, mdims)
     _check(ok, "flash_attn_bwd")
     return dq, dk, dv
 
@@ -198,7 +211,8 @@ def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seql
                           softmax_scale: Optional[float] = None, is_causal: bool = False,
                           deterministic: bool = False, seed: int = 0, offset: int = 0, scratch=None,
                           grads: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
-                          stream: Optional[torch.cuda.Stream] = None):
+                          stream: Optional[torch.cuda.Stream] = None, attn_mask: Optional[torch.Tensor] = None,
+                          batch_base: int = 0):
     """Packed backward; returns (dq, dk, dv)."""
     for t in (dout, q, k, v, out):
         assert t.is_cuda and t.is_contiguous()
@@ -209,23 +223,19 @@ def flash_attn_varlen_bwd(dout, q, k, v, out, softmax_lse, cu_seqlens_q, cu_seql
     sq_r, sk_r, d_r = round_up(max_seqlen_q, 128), round_up(max_seqlen_k, 128), round_up(d, 32)
     softmax_d, dq_accum = scratch if scratch is not None else _bwd_scratch(b, sq_r, h, d_r, q.device)
     dq, dk, dv = grads if grads is not None else (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
-    ok = lib().flash_attn_varlen_bwd(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
-                                     _ptr(softmax_lse), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), None,
-                                     _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum), b, max_seqlen_q,
-                                     max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
-                                     1.0 / scale if scale != 0 else 0.0, is_causal,
-                                     q.dtype == torch.bfloat16, 1 if deterministic else 0,
-                                     _stream_ptr(stream), seed, offset, None, None)
+    mptr, mdims, _keep = _mask_args(attn_mask)
+    ok = _call("flash_attn_varlen_bwd", batch_base, _ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_d),
+               _ptr(softmax_lse), _ptr(cu_seqlens_q), _ptr(cu_seqlens_k), None,
+               _ptr(dq), _ptr(dk), _ptr(dv), _ptr(dq_accum), b, max_seqlen_q,
+               max_seqlen_k, sq_r, sk_r, h, hk, d, d_r, p_dropout, scale,
+               1.0 / scale if scale != 0 else 0.0, is_causal,
+               q.dtype == torch.bfloat16, 1 if deterministic else 0,
+               _stream_ptr(stream), seed, offset, mptr, mdims)
     _check(ok, "flash_attn_varlen_bwd")
     return dq, dk, dv
 
 
 # ---- extensions beside the reference ABI (include/flash_attn_b200_ext.h) ---------------------
-
-def set_batch_base(batch_base: int) -> None:
-    """Global index of local batch 0 (keeps dropout masks identical under batch sharding)."""
-    lib().flash_attn_b200_set_batch_base(int(batch_base))
-
 
 _i64 = ctypes.c_int64
 

@@ -19,7 +19,6 @@ thread_local std::string g_error;
 thread_local int g_path_request = FA_B200_PATH_AUTO;
 thread_local int g_last_path = 0;
 thread_local int g_last_launches = 0;
-thread_local int g_batch_base = 0;
 
 bool fail(const char *fmt, ...) __attribute__((format(printf, 1, 2)));
 bool fail(const char *fmt, ...) {
@@ -47,7 +46,7 @@ struct Shape {
 bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout, float softmax_scale,
                  bool is_causal, bool is_bf16, uint64_t seed, uint64_t offset,
                  const int32_t *cu_q, const int32_t *cu_k, bool varlen, const void *attn_mask,
-                 const int64_t *mask_dims) {
+                 const int64_t *mask_dims, int batch_base) {
   if (s.b < 0 || s.sq < 0 || s.sk < 0) return fail("%s: negative batch_size or seqlen", fn);
   if (s.h <= 0 || s.hk <= 0) return fail("%s: num_heads and num_heads_k must be positive", fn);
   if (s.h % s.hk) return fail("%s: num_heads (%d) must be a multiple of num_heads_k (%d)", fn, s.h, s.hk);
@@ -57,6 +56,7 @@ bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout,
   if (!std::isfinite(softmax_scale)) return fail("%s: softmax_scale must be finite", fn);
   if (varlen && (!cu_q || !cu_k)) return fail("%s: cu_seqlens_q / cu_seqlens_k must not be NULL", fn);
   if (s.b > 65535) return fail("%s: batch_size > 65535 is not supported", fn);
+  if (batch_base < 0) return fail("%s: batch_base must not be negative", fn);
   std::memset(&p, 0, sizeof(p));
   p.b = s.b; p.sq = s.sq; p.sk = s.sk; p.sq_rounded = s.sq_r; p.sk_rounded = s.sk_r;
   p.h = s.h; p.hk = s.hk; p.d = s.d; p.d_rounded = s.d_r;
@@ -64,7 +64,7 @@ bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout,
   p.p_dropout = p_dropout;
   p.rp_dropout = fa_dropout_rescale(p_dropout);
   p.drop_threshold = fa_dropout_threshold(p_dropout);
-  p.batch_base = g_batch_base;
+  p.batch_base = batch_base;
   p.seed = seed; p.offset = offset;
   p.causal = is_causal; p.is_bf16 = is_bf16;
   p.cu_q = varlen ? cu_q : nullptr;
@@ -85,10 +85,10 @@ bool fwd_impl(const char *fn, const void *q, const void *k, const void *v, const
               const int32_t *cu_k, bool varlen, void *rng_state, void *out, void *softmax_ptr,
               void *softmax_lse_ptr, const Shape &s, float p_dropout, float softmax_scale,
               bool is_causal, bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
-              uint64_t offset, const void *attn_mask, const int64_t *mask_dims) {
+              uint64_t offset, const void *attn_mask, const int64_t *mask_dims, int batch_base = 0) {
   fa::Params p;
   if (!fill_common(p, fn, s, p_dropout, softmax_scale, is_causal, is_bf16, seed, offset, cu_q, cu_k,
-                   varlen, attn_mask, mask_dims))
+                   varlen, attn_mask, mask_dims, batch_base))
     return false;
   const bool empty = s.b == 0 || s.sq == 0;
   if (!empty && (!q || !k || !v || !out || !softmax_lse_ptr))
@@ -105,16 +105,16 @@ bool fwd_impl(const char *fn, const void *q, const void *k, const void *v, const
   p.softmax_ret = return_softmax ? softmax_ptr : nullptr;
 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool tc_ok = !empty && fa::tc_fwd_supported(p);
+  if (!empty && g_path_request == FA_B200_PATH_TCGEN05 && !tc_ok)
+    return fail("%s: tcgen05 path requested but this problem is outside it", fn);
+  // every check has passed: only now is caller memory written
   int launches = 0;
   if (rng_state) {
     write_rng_state_kernel<<<1, 1, 0, st>>>(static_cast<uint64_t *>(rng_state), seed, offset);
     ++launches;
   }
   if (empty) { g_last_launches = launches; return true; }
-
-  const bool tc_ok = fa::tc_fwd_supported(p);
-  if (g_path_request == FA_B200_PATH_TCGEN05 && !tc_ok)
-    return fail("%s: tcgen05 path requested but this problem is outside it", fn);
   const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
   const char *err = use_tc ? fa::launch_tc_fwd(p, st) : fa::launch_generic_fwd(p, st);
   if (err) return fail("%s: %s", fn, err);
@@ -128,10 +128,10 @@ bool bwd_impl(const char *fn, const void *dout, const void *q, const void *k, co
               const int32_t *cu_k, bool varlen, void *dq, void *dk, void *dv, void *dq_accum,
               const Shape &s, float p_dropout, float softmax_scale, bool is_causal, bool is_bf16,
               int num_splits, fa_stream_t stream, uint64_t seed, uint64_t offset,
-              const void *attn_mask, const int64_t *mask_dims) {
+              const void *attn_mask, const int64_t *mask_dims, int batch_base = 0) {
   fa::Params p;
   if (!fill_common(p, fn, s, p_dropout, softmax_scale, is_causal, is_bf16, seed, offset, cu_q, cu_k,
-                   varlen, attn_mask, mask_dims))
+                   varlen, attn_mask, mask_dims, batch_base))
     return false;
   if (s.b == 0) { g_last_launches = 0; return true; }
   if (!dout || !q || !k || !v || !out || !softmax_d || !softmax_lse || !dq || !dk || !dv)
@@ -152,7 +152,8 @@ bool bwd_impl(const char *fn, const void *dout, const void *q, const void *k, co
   if (g_path_request == FA_B200_PATH_TCGEN05 && !tc_ok)
     return fail("%s: tcgen05 path requested but this problem is outside it", fn);
   const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
-  const char *err = fa::launch_bwd_preprocess(p, st);
+  // softmax_d; the tcgen05 backward's dq_accum is zeroed by the same kernel
+  const char *err = fa::launch_bwd_preprocess(p, st, use_tc ? p.dq_accum : nullptr, use_tc ? fa::tc_bwd_scratch_floats(p) : 0);
   if (!err) err = use_tc ? fa::launch_tc_bwd(p, st) : fa::launch_generic_bwd(p, st);
   if (err) return fail("%s: %s", fn, err);
   g_last_path = use_tc ? FA_B200_PATH_TCGEN05 : FA_B200_PATH_GENERIC;
@@ -275,9 +276,90 @@ void flash_attn_set_error(const char *msg) {
 // Replaces reference flash_attn.h:138.
 const char *flash_attn_error(void) { return g_error.c_str(); }
 
+
+// ---- batch-shard entry points (include/flash_attn_b200_ext.h): the reference calls plus an explicit batch_base --------
+bool flash_attn_b200_fwd_shard(int batch_base, const void *q, const void *k, const void *v, void *rng_state, void *out,
+                               void *softmax_ptr, void *softmax_lse_ptr, int batch_size, int seqlen_q, int seqlen_k,
+                               int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size,
+                               int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale,
+                               bool is_causal, bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
+                               uint64_t offset, const void *attn_mask, const int64_t *mask_dims) {
+  (void)softmax_unscale;
+  try {
+    const Shape s{batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return fwd_impl("flash_attn_b200_fwd_shard", q, k, v, nullptr, nullptr, false, rng_state, out, softmax_ptr,
+                    softmax_lse_ptr, s, p_dropout, softmax_scale, is_causal, return_softmax, is_bf16, stream, seed,
+                    offset, attn_mask, mask_dims, batch_base);
+  } catch (...) {
+    return fail("flash_attn_b200_fwd_shard: unexpected exception");
+  }
+}
+
+bool flash_attn_b200_varlen_fwd_shard(int batch_base, const void *q, const void *k, const void *v,
+                                      const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, void *rng_state,
+                                      void *out, void *softmax_ptr, void *softmax_lse_ptr, int batch_size,
+                                      int max_seqlen_q, int max_seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded,
+                                      int num_heads, int num_heads_k, int head_size, int head_size_rounded,
+                                      float p_dropout, float softmax_scale, float softmax_unscale, bool is_causal,
+                                      bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
+                                      uint64_t offset, const void *attn_mask, const void *mask_dims) {
+  (void)softmax_unscale;
+  try {
+    const Shape s{batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return fwd_impl("flash_attn_b200_varlen_fwd_shard", q, k, v, cu_seqlens_q, cu_seqlens_k, true, rng_state, out,
+                    softmax_ptr, softmax_lse_ptr, s, p_dropout, softmax_scale, is_causal, return_softmax, is_bf16,
+                    stream, seed, offset, attn_mask, static_cast<const int64_t *>(mask_dims), batch_base);
+  } catch (...) {
+    return fail("flash_attn_b200_varlen_fwd_shard: unexpected exception");
+  }
+}
+
+bool flash_attn_b200_bwd_shard(int batch_base, const void *dout, const void *q, const void *k, const void *v,
+                               const void *out, const void *softmax_d, const void *softmax_lse, void *rng_state,
+                               void *dq, void *dk, void *dv, void *dq_accum, int batch_size, int seqlen_q, int seqlen_k,
+                               int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size,
+                               int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale,
+                               bool is_causal, bool is_bf16, int num_splits, fa_stream_t stream, uint64_t seed,
+                               uint64_t offset, const void *attn_mask, const int64_t *mask_dims) {
+  (void)softmax_unscale;
+  (void)rng_state;
+  try {
+    const Shape s{batch_size, seqlen_q, seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return bwd_impl("flash_attn_b200_bwd_shard", dout, q, k, v, out, softmax_d, softmax_lse, nullptr, nullptr, false,
+                    dq, dk, dv, dq_accum, s, p_dropout, softmax_scale, is_causal, is_bf16, num_splits, stream, seed,
+                    offset, attn_mask, mask_dims, batch_base);
+  } catch (...) {
+    return fail("flash_attn_b200_bwd_shard: unexpected exception");
+  }
+}
+
+bool flash_attn_b200_varlen_bwd_shard(int batch_base, const void *dout, const void *q, const void *k, const void *v,
+                                      const void *out, const void *softmax_d, const void *softmax_lse,
+                                      const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, void *rng_state,
+                                      void *dq, void *dk, void *dv, void *dq_accum, int batch_size, int max_seqlen_q,
+                                      int max_seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded, int num_heads,
+                                      int num_heads_k, int head_size, int head_size_rounded, float p_dropout,
+                                      float softmax_scale, float softmax_unscale, bool is_causal, bool is_bf16,
+                                      int num_splits, fa_stream_t stream, uint64_t seed, uint64_t offset,
+                                      const void *attn_mask, const int64_t *mask_dims) {
+  (void)softmax_unscale;
+  (void)rng_state;
+  try {
+    const Shape s{batch_size, max_seqlen_q, max_seqlen_k, seqlen_q_rounded, seqlen_k_rounded,
+                  num_heads, num_heads_k, head_size, head_size_rounded};
+    return bwd_impl("flash_attn_b200_varlen_bwd_shard", dout, q, k, v, out, softmax_d, softmax_lse, cu_seqlens_q,
+                    cu_seqlens_k, true, dq, dk, dv, dq_accum, s, p_dropout, softmax_scale, is_causal, is_bf16,
+                    num_splits, stream, seed, offset, attn_mask, mask_dims, batch_base);
+  } catch (...) {
+    return fail("flash_attn_b200_varlen_bwd_shard: unexpected exception");
+  }
+}
+
 void flash_attn_b200_set_path(int path) { g_path_request = path; }
 int flash_attn_b200_last_path(void) { return g_last_path; }
-void flash_attn_b200_set_batch_base(int batch_base) { g_batch_base = batch_base; }
 int flash_attn_b200_last_launch_count(void) { return g_last_launches; }
 int flash_attn_b200_trace_read(int kernel, int role, unsigned long long *dst, int max_events) {
   return kernel == 0 ? fa::trace_read_fwd(dst, role, max_events) : fa::trace_read_bwd(dst, role, max_events);

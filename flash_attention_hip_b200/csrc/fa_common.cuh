@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "philox_spec.h"
 
 namespace fa {
@@ -84,10 +86,86 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ---- per-device launch state ------------------------------------------------------------------------
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) and the SM count belong to a DEVICE, not to the process:
+// a caller may drive several GPUs from one process (one host thread per device, cudaSetDevice before the
+// call -- INTEGRATION.md), so both are cached per device ordinal, lock-free (re-doing either is harmless).
+constexpr int kMaxCachedDevices = 64;
+
+// Current device and its SM count.  Returns nullptr or a static error string.
+inline const char *current_device(int *dev, int *sm_count) {
+  static std::atomic<int> cache[kMaxCachedDevices];     // zero-initialised
+  if (cudaGetDevice(dev) != cudaSuccess) return "cudaGetDevice failed";
+  int c = (*dev >= 0 && *dev < kMaxCachedDevices) ? cache[*dev].load(std::memory_order_relaxed) : 0;
+  if (c <= 0) {
+    if (cudaDeviceGetAttribute(&c, cudaDevAttrMultiProcessorCount, *dev) != cudaSuccess || c <= 0)
+      return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
+    if (*dev >= 0 && *dev < kMaxCachedDevices) cache[*dev].store(c, std::memory_order_relaxed);
+  }
+  *sm_count = c;
+  return nullptr;
+}
+
+// Opt one kernel instantiation into `bytes` of dynamic shared memory on device `dev`, once per device.
+// `done` is that instantiation's bit set (a function-local static of the launcher template).
+template <typename Kernel>
+inline const char *ensure_dynamic_smem(Kernel kern, int bytes, int dev, std::atomic<uint64_t> &done) {
+  const bool cached = dev >= 0 && dev < kMaxCachedDevices;
+  if (cached && ((done.load(std::memory_order_acquire) >> dev) & 1ull)) return nullptr;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
+    return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
+  if (cached) done.fetch_or(1ull << dev, std::memory_order_release);
+  return nullptr;
+}
+
+// Work-item counters of the persistent kernels: a pool of self-resetting {next item, CTAs done} pairs in
+// device memory (one pool per kernel family and device).  A launch takes the next slot round-robin; the
+// last CTA to leave the item loop zeroes the pair again, so a launch needs no allocation, memset or free
+// (the ABI has no argument for scratch of this kind).  Two launches share a slot only if kSchedSlots other
+// launches of the same family were issued between them AND both are resident at once, which kernels that
+// fill every SM cannot be.
+constexpr int kSchedSlots = 64;
+struct SchedSlot { int next, done, pad[2]; };
+inline int next_sched_slot(std::atomic<unsigned> &ticket) {
+  return (int)(ticket.fetch_add(1u, std::memory_order_relaxed) % (unsigned)kSchedSlots);
+}
+// Host: this launch's slot of the pool behind device symbol `pool_symbol` (address cached per device).
+template <typename Symbol>
+inline const char *take_sched_slot(const Symbol &pool_symbol, int dev, std::atomic<SchedSlot *> *cache,
+                                   std::atomic<unsigned> &ticket, SchedSlot **out) {
+  const bool cached = dev >= 0 && dev < kMaxCachedDevices;
+  SchedSlot *pool = cached ? cache[dev].load(std::memory_order_acquire) : nullptr;
+  if (!pool) {
+    if (cudaGetSymbolAddress(reinterpret_cast<void **>(&pool), pool_symbol) != cudaSuccess || !pool)
+      return "cudaGetSymbolAddress(item counters) failed";
+    if (cached) cache[dev].store(pool, std::memory_order_release);
+  }
+  *out = pool + next_sched_slot(ticket);
+  return nullptr;
+}
+#ifdef __CUDACC__
+// Scheduler lane of a persistent CTA: the next item, or -1 once the items have run out (called exactly
+// once with that outcome per CTA: the last CTA to see it re-arms the slot for a later launch).
+__device__ __forceinline__ int sched_next_item(SchedSlot *slot, int n_items) {
+  const int L = atomicAdd(&slot->next, 1);
+  if (L < n_items) return L;
+  __threadfence();                                  // my last pull is ordered before my `done` count
+  if (atomicAdd(&slot->done, 1) == (int)gridDim.x - 1) {
+    slot->next = 0;
+    slot->done = 0;
+    __threadfence();
+  }
+  return -1;
+}
+#endif
+
 // Launchers (defined in the .cu files; all asynchronous on `stream`).
 const char *launch_generic_fwd(const Params &p, cudaStream_t stream);
 const char *launch_generic_bwd(const Params &p, cudaStream_t stream);
-const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream);
+// softmax_d = rowsum(dout o out); also zeroes `zero_floats` floats at `zero_acc` (the tcgen05 backward's dq_accum) when non-null
+const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream, float *zero_acc, long long zero_floats);
+// floats of dq_accum the tcgen05 backward uses: [b][h][query tiles][ceil(d/32)][128][32]
+long long tc_bwd_scratch_floats(const Params &p);
 // all-shapes backward on warp-level MMAs (fa_mma_bwd.cu); what launch_generic_bwd runs
 const char *launch_mma_bwd(const Params &p, cudaStream_t stream);
 

@@ -268,13 +268,12 @@ const char *launch_t(const Params &p, cudaStream_t stream) {
   using S = Smem<kD>;
   auto kq = mma_bwd_dq_kernel<T, kD>;
   auto kk = mma_bwd_dkdv_kernel<T, kD>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes) != cudaSuccess ||
-        cudaFuncSetAttribute(kk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::kBytes) != cudaSuccess)
-      return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
-    attr_set = true;
-  }
+  int dev = 0, sm_count = 0;
+  const char *de;
+  if ((de = current_device(&dev, &sm_count))) return de;
+  static std::atomic<uint64_t> opt_q{0}, opt_k{0};   // per instantiation, one bit per device
+  if ((de = ensure_dynamic_smem(kq, (int)S::kBytes, dev, opt_q))) return de;
+  if ((de = ensure_dynamic_smem(kk, (int)S::kBytes, dev, opt_k))) return de;
   if (p.sq > 0) kq<<<dim3((p.sq + kB - 1) / kB, p.h, p.b), kThreads, S::kBytes, stream>>>(p);
   if (p.sk > 0) kk<<<dim3((p.sk + kB - 1) / kB, p.hk, p.b), kThreads, S::kBytes, stream>>>(p);
   const cudaError_t e = cudaGetLastError();

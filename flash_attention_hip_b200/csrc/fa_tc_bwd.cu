@@ -41,6 +41,7 @@ namespace {
 constexpr int kBwdSyncGroups = FA_BWD_SYNC_GROUPS;   // dropout: scheduling block = this many groups of 8 exponentials + 5 Philox rounds
 // Every n-th group of four exponentials computes one pair on the FMA pipe instead of MUFU (0 = never).
 constexpr int kBwdEmuEvery = FA_BWD_EMU_EVERY;
+constexpr int kPhiloxSteps = 4 * FA_PHILOX_ROUNDS;   // round steps of an iteration's four calls, spread over its 8 groups
 constexpr int kT = 128;            // tile edge: keys per CTA tile, queries per inner tile
 constexpr int kThreads = 512;
 constexpr int kMmaWarp = 8, kLoadWarp = 9, kDrainWarp0 = 12;
@@ -65,6 +66,7 @@ struct Cfg {
   static_assert(kBytes > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
 
+__device__ SchedSlot g_bwd_sched[kSchedSlots];       // item counters of the persistent launches (fa_common.cuh)
 __device__ ptx::TensorMapSlot g_bwd_slots[ptx::kMaxSm][2][6];   // two alternating sets (packed inputs)
 
 struct BwdArgs {
@@ -84,7 +86,7 @@ struct BwdArgs {
   int causal;
   int nkt, n_items;      // key tiles per sequence (dense: of sk; packed: of the longest); items = nkt * hk * b
   int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
-  int *sched;            // global item counter (stream-ordered temporary, zeroed before the launch)
+  SchedSlot *sched;      // global item counter of this launch (self-resetting pool slot, fa_common.cuh)
 };
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi, bool bf16) {
@@ -298,8 +300,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if (lane == 0) {
         const int slot = n & 1;
         if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
-        L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
-        if (L >= a.n_items) L = -1;
+        L = a.persistent ? sched_next_item(a.sched, a.n_items) : (n == 0 ? (int)blockIdx.x : -1);
         sched_item[slot] = L;
         ptx::mbar_arrive(B.sched_full + 8 * slot);
       }
@@ -742,7 +743,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           if (c % 8 == 4) {               // a group = 8 exponentials + 5 Philox rounds, round-robin over the calls
             const int g = c / 8;
 #pragma unroll
-            for (int k = 5 * g; k < 5 * g + 5; ++k) fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
+            for (int k = kPhiloxSteps * g / 8; k < kPhiloxSteps * (g + 1) / 8; ++k)
+              fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
             // nvvm would sink the rounds to their use and ptxas below the last exponential (a warp issues in
             // order: they would run after the MUFU stream, not under it): laundering pins them to this
             // group, __syncwarp() ends ptxas's scheduling block
@@ -883,6 +885,9 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
   }
 }
 
+std::atomic<SchedSlot *> g_bwd_sched_addr[kMaxCachedDevices];   // device address of g_bwd_sched, per device
+std::atomic<unsigned> g_bwd_ticket{0};
+
 template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
 const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
@@ -915,49 +920,38 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.ctr3 = (uint32_t)p.offset;
   a.causal = p.causal ? 1 : 0;
 
-  const size_t acc_bytes = (size_t)p.b * p.h * a.nqt * kT * a.nblk * 32 * sizeof(float);
-  if (cudaMemsetAsync(p.dq_accum, 0, acc_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq_accum) failed";
-  // num_splits == 1: turn counters for the ordered dQ accumulation, a stream-ordered temporary (the
-  // ABI has no argument for them; freed on the same stream right after the kernel)
-  a.sem = nullptr;
-  if (kOrdered) {
-    const size_t sem_bytes = (size_t)p.b * p.h * a.nqt * sizeof(int);
-    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sem), sem_bytes, stream) != cudaSuccess)
-      return "cudaMallocAsync(dq turn counters) failed";
-    if (cudaMemsetAsync(a.sem, 0, sem_bytes, stream) != cudaSuccess) return "cudaMemsetAsync(dq turn counters) failed";
-  }
-
   auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask, kOrdered>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kBytes) != cudaSuccess)
-      return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
-    attr_set = true;
-  }
+  int dev = 0, sm_count = 0;
+  if ((e = current_device(&dev, &sm_count))) return e;
+  static std::atomic<uint64_t> smem_opt_in{0};   // per instantiation, one bit per device
+  if ((e = ensure_dynamic_smem(kern, (int)C::kBytes, dev, smem_opt_in))) return e;
   a.nkt = (p.sk + kT - 1) / kT;
   a.n_items = a.nkt * p.hk * p.b;
-  static int sm_count = 0;
-  if (!sm_count) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-      return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
-  }
   // ordered dQ: its turns assume CTA j starts after CTAs 0..j-1; no more items than SMs: no counter needed
   a.persistent = (!kOrdered && a.n_items > sm_count) ? 1 : 0;
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
     grid = sm_count;
-    // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
-    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
-      return "cudaMallocAsync(item counter) failed";
-    if (cudaMemsetAsync(a.sched, 0, sizeof(int), stream) != cudaSuccess) return "cudaMemsetAsync(item counter) failed";
+    if ((e = take_sched_slot(g_bwd_sched, dev, g_bwd_sched_addr, g_bwd_ticket, &a.sched))) return e;
+  }
+
+  // (dq_accum was zeroed by the preprocess kernel: tc_bwd_scratch_floats)
+  // num_splits == 1: turn counters for the ordered dQ accumulation, a stream-ordered temporary (the
+  // ABI has no argument for them; freed on the same stream right after the kernel, on every exit)
+  a.sem = nullptr;
+  if (kOrdered) {
+    const size_t sem_bytes = (size_t)p.b * p.h * a.nqt * sizeof(int);
+    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sem), sem_bytes, stream) != cudaSuccess)
+      return "cudaMallocAsync(dq turn counters) failed";
+    if (cudaMemsetAsync(a.sem, 0, sem_bytes, stream) != cudaSuccess) {
+      cudaFreeAsync(a.sem, stream);
+      return "cudaMemsetAsync(dq turn counters) failed";
+    }
   }
   kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, tdk, tdv, a);
   cudaError_t err = cudaGetLastError();
   if (a.sem) cudaFreeAsync(a.sem, stream);
-  if (a.sched) cudaFreeAsync(a.sched, stream);
   if (err != cudaSuccess) return cudaGetErrorString(err);
   dim3 cgrid(a.nqt, p.h, p.b);
   dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale * p.rp_dropout, a.d,
@@ -975,6 +969,10 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
   (void)dst; (void)role; (void)max_events;
   return 0;
 #endif
+}
+
+long long tc_bwd_scratch_floats(const Params &p) {
+  return (long long)p.b * p.h * ((p.sq + kT - 1) / kT) * kT * ((p.d + 31) / 32) * 32;
 }
 
 bool tc_bwd_supported(const Params &p) {

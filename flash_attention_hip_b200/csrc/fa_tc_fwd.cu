@@ -46,12 +46,14 @@ constexpr int kEmuPer8 = FA_EMU_PER8;
 #ifndef FA_FWD_SYNC_GROUPS
 #define FA_FWD_SYNC_GROUPS 2
 #endif
-// Dropout: a scheduling block of the softmax loop = this many groups of (8 exponentials + 5 Philox rounds).
+// Dropout: a scheduling block of the softmax loop = this many groups of (8 exponentials + 3-4 Philox rounds; 5 when
+// the generator had 10 rounds, which is what the figures below were measured with).
 // ptxas orders instructions freely inside a block and a warp issues in order, so the block size decides how
 // well the integer work hides under the MUFU stream.  Measured on B200 (C3 forward, dropout 0.1):
 // whole tile 710, 4 groups 778, 3 groups 811, 2 groups 818, 1 group 747 TFLOP/s (660 with the draws after S arrived).
 constexpr int kSyncGroups = FA_FWD_SYNC_GROUPS;
-static_assert(FA_PHILOX_ROUNDS == 10, "the forward steps 4 calls x 10 rounds over 8 groups of exponentials");
+// The draw-ahead loop spreads 4 calls x FA_PHILOX_ROUNDS rounds over the 8 groups of a 64-column half.
+constexpr int kPhiloxSteps = 4 * FA_PHILOX_ROUNDS;
 #ifndef FA_FWD_APPLY_IN_GROUP
 #define FA_FWD_APPLY_IN_GROUP 0
 #endif
@@ -95,6 +97,8 @@ constexpr bool stage_o(bool dropout) {
   return !dropout;
 #endif
 }
+
+__device__ SchedSlot g_fwd_sched[kSchedSlots];       // item counters of the persistent launches (fa_common.cuh)
 
 // Per-SM homes of the tensor maps a CTA bounds to its own sequence (packed inputs only).
 __device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][2][3];   // two sets: the next sequence's maps are built while the previous ones are in use
@@ -160,7 +164,7 @@ struct TcFwdArgs {
   int causal;
   int nqb, n_items;      // query blocks per (batch, head); work items = nqb * h * b
   int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
-  int *sched;            // global item counter (stream-ordered temporary, zeroed before the launch)
+  SchedSlot *sched;      // global item counter of this launch (self-resetting pool slot, fa_common.cuh)
   // O addressing of the staged epilogue, in elements: out + batch * o_batch + row * o_row + head * o_head
   // (dense default: sq*h*d, h*d, d; the GQA-packed decode view swaps the roles of heads and rows)
   long long o_batch, o_row, o_head;
@@ -304,8 +308,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (lane == 0) {
           const int slot = n & 1;
           if (n >= 2) ptx::mbar_wait(B.sched_empty + 8 * slot, ((n >> 1) - 1) & 1);
-          L = a.persistent ? atomicAdd(a.sched, 1) : (n == 0 ? (int)blockIdx.x : a.n_items);
-          if (L >= a.n_items) L = -1;
+          L = a.persistent ? sched_next_item(a.sched, a.n_items) : (n == 0 ? (int)blockIdx.x : -1);
           sched_item[slot] = L;
           ptx::mbar_arrive(B.sched_full + 8 * slot);
         }
@@ -691,7 +694,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               }
             }
 #pragma unroll
-            for (int k = 5 * g; k < 5 * g + 5; ++k) fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
+            for (int k = kPhiloxSteps * g / 8; k < kPhiloxSteps * (g + 1) / 8; ++k)
+              fa_philox_round(pc[k % 4], a.key0, a.key1, k / 4);
             // nvvm would sink the rounds to their use; ptxas would sink them below the tile's last
             // exponential.  Laundering pins them to this group, __syncwarp() ends ptxas's scheduling block.
 #pragma unroll
@@ -712,7 +716,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         // every 8 exponentials on the FMA pipe pay (635 -> 690 TFLOP/s at S4096 causal, 679 -> 780 without the mask,
         // varlen mix 480 -> 520-580; host switch a.use_emu: off below 1536 keys); at D = 128 they gain
         // 4 % at S4096 but lose 2 % at S2048, and with dropout they wreck the draw-ahead schedule (881 -> 629)
-        constexpr int kEmu = (kEmuPer8 == 0 && D == 64 && !kDropout) ? 4 : kEmuPer8;
+        constexpr int kEmu = kMask ? 0 : (kEmuPer8 == 0 && D == 64 && !kDropout) ? 4 : kEmuPer8;   // a bias may hold -inf: ex2_poly2 would give 2^-125, not 0
         if (kEmu == 0 || need_mask || !a.use_emu) exp_half(std::integral_constant<int, 0>{}, half);
         else exp_half(std::integral_constant<int, kEmu>{}, half);
         if constexpr (kDropout) {
@@ -873,6 +877,9 @@ bool tc_fwd_supported(const Params &p) {
 
 namespace {
 
+std::atomic<SchedSlot *> g_fwd_sched_addr[kMaxCachedDevices];   // device address of g_fwd_sched, per device
+std::atomic<unsigned> g_fwd_ticket{0};
+
 template <int D, bool kBF16, bool kDropout, bool kMask>
 const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
@@ -916,35 +923,22 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.use_emu = p.sk >= 1536 ? 1 : 0;
 
   auto kern = tc_fwd_kernel<D, kBF16, kDropout, kMask>;
-  static bool attr_set = false;   // per instantiation
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes(stage_o(kDropout))) != cudaSuccess)
-      return "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed";
-    attr_set = true;
-  }
+  int dev = 0, sm_count = 0;
+  if ((e = current_device(&dev, &sm_count))) return e;
+  static std::atomic<uint64_t> smem_opt_in{0};   // per instantiation, one bit per device
+  if ((e = ensure_dynamic_smem(kern, (int)C::smem_bytes(stage_o(kDropout)), dev, smem_opt_in))) return e;
   a.nqb = (sq_eff + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
   a.n_items = a.nqb * h_eff * p.b;
-  static int sm_count = 0;
-  if (!sm_count) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm_count <= 0)
-      return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
-  }
-  // no more items than SMs: one item per CTA needs no counter (and no allocation / memset on a latency-bound call)
+  // no more items than SMs: one item per CTA, no counter
   a.persistent = a.n_items > sm_count ? 1 : 0;
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
     grid = sm_count;
-    // the ABI has no argument for the item counter: a stream-ordered temporary, freed right after the kernel
-    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sched), sizeof(int), stream) != cudaSuccess)
-      return "cudaMallocAsync(item counter) failed";
-    if (cudaMemsetAsync(a.sched, 0, sizeof(int), stream) != cudaSuccess) return "cudaMemsetAsync(item counter) failed";
+    if ((e = take_sched_slot(g_fwd_sched, dev, g_fwd_sched_addr, g_fwd_ticket, &a.sched))) return e;
   }
   kern<<<grid, kThreads, C::smem_bytes(stage_o(kDropout)), stream>>>(tq, tk, tv, a);
   const cudaError_t err = cudaGetLastError();
-  if (a.sched) cudaFreeAsync(a.sched, stream);
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
 }
 

@@ -8,7 +8,11 @@
  * RNG mapping"); "bit-exact dropout" means: every implementation in this repo
  * reproduces fa_dropout_keep() below for every (b, h, row, col).
  *
- * Generator: Philox-4x32-10 (Salmon et al., SC'11), standard constants.
+ * Generator: Philox-4x32-7 (Salmon et al., SC'11; standard constants; 7 rounds is the fewest
+ * Random123 documents as passing BigCrush, and the round count upstream FlashAttention-2's own
+ * philox.cuh uses).  Round 1 of this repo used 10 rounds: the mapping is this repo's decision --
+ * the reference header pins none -- and 7 rounds cost 30 % less integer work in the softmax warps.
+ * fa_philox4x32_r() takes the round count so that the known-answer tests pin 7 AND 10 rounds.
  *
  * Mapping, on ABSOLUTE coordinates so it cannot depend on tile shapes or
  * thread layouts:
@@ -41,7 +45,7 @@
 #define FA_PHILOX_W0 0x9E3779B9u
 #define FA_PHILOX_W1 0xBB67AE85u
 #ifndef FA_PHILOX_ROUNDS
-#define FA_PHILOX_ROUNDS 10
+#define FA_PHILOX_ROUNDS 7
 #endif
 #define FA_DROPOUT_COLS_PER_CALL 16
 
@@ -57,13 +61,19 @@ FA_HD void fa_philox_round(uint32_t c[4], uint32_t k0, uint32_t k1, int r) {
   c[0] = n0; c[1] = (uint32_t)p1; c[2] = n2; c[3] = (uint32_t)p0;
 }
 
-/* Philox-4x32 with FA_PHILOX_ROUNDS rounds. */
-FA_HD fa_philox4_t fa_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                 uint32_t k0, uint32_t k1) {
+/* Philox-4x32 with `rounds` rounds. */
+FA_HD fa_philox4_t fa_philox4x32_r(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                   uint32_t k0, uint32_t k1, int rounds) {
   fa_philox4_t out;
   out.v[0] = c0; out.v[1] = c1; out.v[2] = c2; out.v[3] = c3;
-  for (int r = 0; r < FA_PHILOX_ROUNDS; ++r) fa_philox_round(out.v, k0, k1, r);
+  for (int r = 0; r < rounds; ++r) fa_philox_round(out.v, k0, k1, r);
   return out;
+}
+
+/* Philox-4x32 with FA_PHILOX_ROUNDS rounds: the generator of the dropout specification. */
+FA_HD fa_philox4_t fa_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                 uint32_t k0, uint32_t k1) {
+  return fa_philox4x32_r(c0, c1, c2, c3, k0, k1, FA_PHILOX_ROUNDS);
 }
 
 /* Keep threshold T in [0, 256]: an entry is kept iff its byte < T. */

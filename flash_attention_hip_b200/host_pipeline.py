@@ -5,7 +5,7 @@ whose tensors live in pinned host memory pays two PCIe transfers around them; si
 units are independent, the batch can be cut into chunks and the three phases overlapped on three
 streams: chunk c+1's host->device copy, chunk c's kernels, chunk c-1's device->host copy (PCIe is
 full duplex, so the two copy directions overlap each other too).  Dropout stays identical to the
-unchunked call through `set_batch_base`.  This is what bench.py's `e2e` figure runs.
+unchunked call through the `batch_base` argument of the `_shard` entry points.  This is what bench.py's `e2e` figure runs.
 """
 from __future__ import annotations
 
@@ -48,22 +48,18 @@ class HostPipelinedAttention:
                     dst[i0:i1].copy_(src[i0:i1], non_blocking=True)
                 ready = self.s_in.record_event()
             self.s_cmp.wait_event(ready)
-            api.set_batch_base(batch_base + i0)
-            try:
-                kw = dict(p_dropout=p_dropout, softmax_scale=scale, is_causal=causal, seed=seed, offset=offset,
-                          stream=self.s_cmp)
-                sd, acc = self.scratch[c & 1]
-                n = i1 - i0
-                # torch's allocator ties lse / rng_state to the stream that is current when they are made
-                with torch.cuda.stream(self.s_cmp):
-                    _, lse, _, _ = api.flash_attn_fwd(self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], out=self.out[i0:i1], **kw)
-                    self.launches += api.last_launch_count()
-                    api.flash_attn_bwd(self.do[i0:i1], self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], self.out[i0:i1], lse,
-                                       scratch=(sd[:n], acc[:n]), grads=(self.dq[i0:i1], self.dk[i0:i1], self.dv[i0:i1]),
-                                       **kw)
-                    self.launches += api.last_launch_count()
-            finally:
-                api.set_batch_base(batch_base)
+            kw = dict(p_dropout=p_dropout, softmax_scale=scale, is_causal=causal, seed=seed, offset=offset,
+                      stream=self.s_cmp, batch_base=batch_base + i0)
+            sd, acc = self.scratch[c & 1]
+            n = i1 - i0
+            # torch's allocator ties lse / rng_state to the stream that is current when they are made
+            with torch.cuda.stream(self.s_cmp):
+                _, lse, _, _ = api.flash_attn_fwd(self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], out=self.out[i0:i1], **kw)
+                self.launches += api.last_launch_count()
+                api.flash_attn_bwd(self.do[i0:i1], self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], self.out[i0:i1], lse,
+                                   scratch=(sd[:n], acc[:n]), grads=(self.dq[i0:i1], self.dk[i0:i1], self.dv[i0:i1]),
+                                   **kw)
+                self.launches += api.last_launch_count()
             done = self.s_cmp.record_event()
             self.s_out.wait_event(done)
             with torch.cuda.stream(self.s_out):

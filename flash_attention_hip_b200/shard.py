@@ -3,8 +3,9 @@
 Every (batch, head) pair is an independent problem and the reference layouts put batch outermost
 (/root/reference/flash_attn.h:10-12), so a rank's shard is a pointer offset and a smaller
 `batch_size` (:17): there is NO data-path collective.  The only cross-rank state is the dropout
-stream, which is indexed by the global batch (csrc/philox_spec.h); `set_batch_base` keeps a shard's
-masks equal to the unsharded call's.
+stream, which is indexed by the global batch (csrc/philox_spec.h); the `batch_base` argument of the
+`flash_attn_b200_*_shard` entry points (include/flash_attn_b200_ext.h) keeps a shard's masks equal to the
+unsharded call's.
 
 `ops` is the compute engine: the C-ABI library by default (`CudaOps`); the CPU tests pass an
 oracle-backed engine so that the host logic runs under gloo without a GPU.
@@ -33,21 +34,13 @@ class CudaOps:
         self.api = api
 
     def fwd(self, q, k, v, *, causal, scale, p_dropout=0.0, seed=0, offset=0, batch_base=0):
-        self.api.set_batch_base(batch_base)
-        try:
-            out, lse, _, _ = self.api.flash_attn_fwd(q, k, v, p_dropout=p_dropout, softmax_scale=scale,
-                                                     is_causal=causal, seed=seed, offset=offset)
-        finally:
-            self.api.set_batch_base(0)
+        out, lse, _, _ = self.api.flash_attn_fwd(q, k, v, p_dropout=p_dropout, softmax_scale=scale,
+                                                 is_causal=causal, seed=seed, offset=offset, batch_base=batch_base)
         return out, lse
 
     def bwd(self, dout, q, k, v, out, lse, *, causal, scale, p_dropout=0.0, seed=0, offset=0, batch_base=0):
-        self.api.set_batch_base(batch_base)
-        try:
-            return self.api.flash_attn_bwd(dout, q, k, v, out, lse, p_dropout=p_dropout, softmax_scale=scale,
-                                           is_causal=causal, seed=seed, offset=offset)
-        finally:
-            self.api.set_batch_base(0)
+        return self.api.flash_attn_bwd(dout, q, k, v, out, lse, p_dropout=p_dropout, softmax_scale=scale,
+                                       is_causal=causal, seed=seed, offset=offset, batch_base=batch_base)
 
     # ring context-parallel combine steps (csrc/fa_cp.cu)
     def merge(self, o_acc, lse_acc, o_blk, lse_blk):

@@ -31,10 +31,43 @@ void flash_attn_b200_set_path(int path);
  * (FA_B200_PATH_GENERIC or FA_B200_PATH_TCGEN05; 0 before any call). */
 int flash_attn_b200_last_path(void);
 
-/* Batch sharding: the dropout stream is indexed by (batch, head, row, column); a rank
- * that holds batches [base, base + n) of a global batch sets `batch_base = base` so that its masks
- * equal the unsharded call's.  Thread-local, sticky, default 0. */
-void flash_attn_b200_set_batch_base(int batch_base);
+/* Batch sharding.  The dropout stream is indexed by (GLOBAL batch, head, row, column); a rank that
+ * holds batches [base, base + n) of a global batch passes `batch_base = base` so that its masks equal the
+ * unsharded call's.  The four functions below are the reference entry points (include/flash_attn.h, reference
+ * flash_attn.h:10-134) with that ONE extra leading argument and otherwise identical arguments, results and
+ * error behaviour; batch_base = 0 is exactly the reference call.  A forward and its backward must be given the
+ * same batch_base.  (Round 1 had a sticky thread-local setter instead; it is gone: hidden per-thread state
+ * beside the ABI is a trap for callers that run on thread pools.) */
+bool flash_attn_b200_fwd_shard(int batch_base, const void *q, const void *k, const void *v, void *rng_state, void *out,
+                               void *softmax_ptr, void *softmax_lse_ptr, int batch_size, int seqlen_q, int seqlen_k,
+                               int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size,
+                               int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale,
+                               bool is_causal, bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
+                               uint64_t offset, const void *attn_mask, const int64_t *mask_dims);
+bool flash_attn_b200_varlen_fwd_shard(int batch_base, const void *q, const void *k, const void *v,
+                                      const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, void *rng_state,
+                                      void *out, void *softmax_ptr, void *softmax_lse_ptr, int batch_size,
+                                      int max_seqlen_q, int max_seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded,
+                                      int num_heads, int num_heads_k, int head_size, int head_size_rounded,
+                                      float p_dropout, float softmax_scale, float softmax_unscale, bool is_causal,
+                                      bool return_softmax, bool is_bf16, fa_stream_t stream, uint64_t seed,
+                                      uint64_t offset, const void *attn_mask, const void *mask_dims);
+bool flash_attn_b200_bwd_shard(int batch_base, const void *dout, const void *q, const void *k, const void *v,
+                               const void *out, const void *softmax_d, const void *softmax_lse, void *rng_state,
+                               void *dq, void *dk, void *dv, void *dq_accum, int batch_size, int seqlen_q, int seqlen_k,
+                               int seqlen_q_rounded, int seqlen_k_rounded, int num_heads, int num_heads_k, int head_size,
+                               int head_size_rounded, float p_dropout, float softmax_scale, float softmax_unscale,
+                               bool is_causal, bool is_bf16, int num_splits, fa_stream_t stream, uint64_t seed,
+                               uint64_t offset, const void *attn_mask, const int64_t *mask_dims);
+bool flash_attn_b200_varlen_bwd_shard(int batch_base, const void *dout, const void *q, const void *k, const void *v,
+                                      const void *out, const void *softmax_d, const void *softmax_lse,
+                                      const int32_t *cu_seqlens_q, const int32_t *cu_seqlens_k, void *rng_state,
+                                      void *dq, void *dk, void *dv, void *dq_accum, int batch_size, int max_seqlen_q,
+                                      int max_seqlen_k, int seqlen_q_rounded, int seqlen_k_rounded, int num_heads,
+                                      int num_heads_k, int head_size, int head_size_rounded, float p_dropout,
+                                      float softmax_scale, float softmax_unscale, bool is_causal, bool is_bf16,
+                                      int num_splits, fa_stream_t stream, uint64_t seed, uint64_t offset,
+                                      const void *attn_mask, const int64_t *mask_dims);
 
 /* Number of kernel launches the last successful call on this thread enqueued. */
 int flash_attn_b200_last_launch_count(void);

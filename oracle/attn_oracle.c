@@ -135,6 +135,13 @@ void fa_oracle_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out
   for (int i = 0; i < 4; ++i) out[i] = r.v[i];
 }
 
+void fa_oracle_philox_r(const uint32_t ctr[4], const uint32_t key[2], int rounds, uint32_t out[4]) {
+  const fa_philox4_t r = fa_philox4x32_r(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1], rounds);
+  for (int i = 0; i < 4; ++i) out[i] = r.v[i];
+}
+
+int fa_oracle_philox_rounds(void) { return FA_PHILOX_ROUNDS; }
+
 int fa_oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

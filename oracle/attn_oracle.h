@@ -56,6 +56,10 @@ typedef struct {
   const uint16_t *attn_mask;     /* additive bias, storage dtype, or NULL */
   int64_t mask_dims[4];          /* {b|1, h|1, sq, sk} */
   int32_t batch_base;            /* global index of batch 0 (dropout stream of a batch shard) */
+  int32_t round_intermediates;   /* 1 = also round P (after dropout) and dS to the storage dtype before their
+                                    GEMMs, as ANY 16-bit tensor-core pipeline must: the "bf16-rounded reference"
+                                    whose error against the exact build calibrates the parity tests' second
+                                    criterion (kernel error <= 2x this build's error).  0 = exact (the oracle). */
 } fa_oracle_params;
 
 /* Forward.  out: storage dtype, same layout as q.  lse: fp32 [b,h,seqlen_q].
@@ -77,8 +81,11 @@ int fa_oracle_bwd(const fa_oracle_params *p, const uint16_t *dout, const uint16_
 void fa_oracle_dropout_mask(uint64_t seed, uint64_t offset, float p_dropout, uint32_t bh,
                             int32_t sq, int32_t sk, uint8_t *mask);
 
-/* Raw Philox-4x32-10, for the known-answer test. */
+/* Raw Philox-4x32 with the specification's round count (csrc/philox_spec.h: 7), and with an explicit
+ * round count, for the known-answer tests (Random123 publishes vectors for 7 and 10 rounds). */
 void fa_oracle_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
+void fa_oracle_philox_r(const uint32_t ctr[4], const uint32_t key[2], int rounds, uint32_t out[4]);
+int fa_oracle_philox_rounds(void);
 
 /* Storage conversions used by the oracle (round-to-nearest-even). */
 uint16_t fa_oracle_f32_to_storage(float x, int is_bf16);

@@ -42,6 +42,7 @@ class _Params(ctypes.Structure):
         ("attn_mask", ctypes.c_void_p),
         ("mask_dims", ctypes.c_int64 * 4),
         ("batch_base", ctypes.c_int32),
+        ("round_intermediates", ctypes.c_int32),
     ]
 
 
@@ -118,6 +119,7 @@ class Problem:
     attn_mask: Optional[np.ndarray] = None      # uint16 storage [mb, mh, sq, sk]
     use_fp64: bool = False
     batch_base: int = 0      # global index of batch 0 when this problem is a batch shard
+    round_intermediates: bool = False   # the "16-bit pipeline" build: P and dS rounded to the storage dtype too
 
     def __post_init__(self):
         if self.softmax_scale is None:
@@ -161,6 +163,7 @@ class Problem:
         p.p_dropout, p.softmax_scale = self.p_dropout, self.softmax_scale
         p.seed, p.offset = self.seed, self.offset
         p.batch_base = self.batch_base
+        p.round_intermediates = int(self.round_intermediates)
         if self.varlen:
             p.cu_seqlens_q = self.cu_seqlens_q.ctypes.data
             p.cu_seqlens_k = self.cu_seqlens_k.ctypes.data
@@ -220,9 +223,17 @@ def dropout_mask(seed: int, offset: int, p_dropout: float, bh: int, sq: int, sk:
     return m
 
 
-def philox(ctr, key) -> np.ndarray:
+def philox(ctr, key, rounds: Optional[int] = None) -> np.ndarray:
+    """Philox-4x32; rounds=None -> the dropout specification's round count (csrc/philox_spec.h)."""
     c = (ctypes.c_uint32 * 4)(*ctr)
     k = (ctypes.c_uint32 * 2)(*key)
     o = (ctypes.c_uint32 * 4)()
-    lib().fa_oracle_philox(c, k, o)
+    if rounds is None:
+        lib().fa_oracle_philox(c, k, o)
+    else:
+        lib().fa_oracle_philox_r(c, k, ctypes.c_int(rounds), o)
     return np.array(list(o), dtype=np.uint32)
+
+
+def philox_rounds() -> int:
+    return int(lib().fa_oracle_philox_rounds())

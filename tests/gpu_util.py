@@ -40,11 +40,46 @@ class Guarded:
             assert bool((raw[self.PAD + n:] == self.BYTE).all()), "write past an output buffer"
 
 
+def oracle_fwd(pb: O.Problem, q, k, v):
+    """(exact oracle forward, the 16-bit-pipeline build's out as f32): the reference and the error baseline of
+    tests/parity.py's second criterion."""
+    import dataclasses
+    ref = O.forward(pb, q, k, v)
+    lp = O.forward(dataclasses.replace(pb, round_intermediates=True), q, k, v)
+    return ref, O.from_storage(lp["out"], pb.is_bf16)
+
+
+def oracle_bwd(pb: O.Problem, dout, q, k, v, out, lse):
+    """(exact oracle backward, {dq, dk, dv} of the 16-bit-pipeline build as f32)."""
+    import dataclasses
+    rb = O.backward(pb, dout, q, k, v, out, lse)
+    lp = O.backward(dataclasses.replace(pb, round_intermediates=True), dout, q, k, v, out, lse)
+    return rb, {t: O.from_storage(lp[t], pb.is_bf16) for t in ("dq", "dk", "dv")}
+
+
+def check_fwd(label, pb, got, ref, lp_out, varlen_lse=False):
+    """All parity criteria (tests/parity.py) on one forward result."""
+    import parity
+    import cases
+    parity.check(label, "out", f32(got["out"], pb), ref["out_f32"], lp_out)
+    if pb.varlen or varlen_lse:      # rows past a sequence's end are unspecified
+        for b, _, sq, _, _ in cases.seq_slices(pb):
+            parity.check_lse(f"{label}[seq {b}]", got["lse"][b, :, :sq], ref["lse"][b, :, :sq])
+    else:
+        parity.check_lse(label, got["lse"], ref["lse"])
+
+
+def check_bwd(label, pb, gb, rb, lp):
+    import parity
+    for t in ("dq", "dk", "dv"):
+        parity.check(label, t, f32(gb[t], pb), rb[t + "_f32"], lp[t] if lp is not None else None)
+
+
 def run_fwd(pb: O.Problem, q, k, v, return_softmax=False):
     """Returns dict(out bits, lse, softmax bits|None, rng_state) from the CUDA library."""
     dq, dk, dv = (to_dev(a, pb.is_bf16) for a in (q, k, v))
     kw = dict(p_dropout=pb.p_dropout, softmax_scale=pb.softmax_scale, is_causal=pb.is_causal,
-              return_softmax=return_softmax, seed=pb.seed, offset=pb.offset)
+              return_softmax=return_softmax, seed=pb.seed, offset=pb.offset, batch_base=pb.batch_base)
     g = Guarded()
     nb = len(pb.cu_seqlens_q) - 1 if pb.varlen else pb.batch
     kw["lse"] = g.make((nb, pb.num_heads, pb.seqlen_q), torch.float32, fill=float("inf"))
@@ -52,7 +87,8 @@ def run_fwd(pb: O.Problem, q, k, v, return_softmax=False):
         cq = torch.from_numpy(pb.cu_seqlens_q).cuda()
         ck = torch.from_numpy(pb.cu_seqlens_k).cuda()
         kw["out"] = g.make(tuple(dq.shape), dq.dtype)
-        out, lse, sm, rng = api.flash_attn_varlen_fwd(dq, dk, dv, cq, ck, pb.seqlen_q, pb.seqlen_k, **kw)
+        mask = None if pb.attn_mask is None else to_dev(pb.attn_mask, pb.is_bf16)
+        out, lse, sm, rng = api.flash_attn_varlen_fwd(dq, dk, dv, cq, ck, pb.seqlen_q, pb.seqlen_k, attn_mask=mask, **kw)
     else:
         shp_q = (pb.batch, pb.seqlen_q, pb.num_heads, pb.head_size)
         shp_k = (pb.batch, pb.seqlen_k, pb.num_heads_k, pb.head_size)
@@ -70,7 +106,7 @@ def run_bwd(pb: O.Problem, dout, q, k, v, out, lse, deterministic=False):
     t = [to_dev(a, pb.is_bf16) for a in (dout, q, k, v, out)]
     lse_d = torch.from_numpy(np.ascontiguousarray(lse, dtype=np.float32)).cuda()
     kw = dict(p_dropout=pb.p_dropout, softmax_scale=pb.softmax_scale, is_causal=pb.is_causal,
-              deterministic=deterministic, seed=pb.seed, offset=pb.offset)
+              deterministic=deterministic, seed=pb.seed, offset=pb.offset, batch_base=pb.batch_base)
     g = Guarded()
     nb = len(pb.cu_seqlens_q) - 1 if pb.varlen else pb.batch
     sq_r, d_r = api.round_up(pb.seqlen_q, 128), api.round_up(pb.head_size, 32)
@@ -81,7 +117,8 @@ def run_bwd(pb: O.Problem, dout, q, k, v, out, lse, deterministic=False):
         ck = torch.from_numpy(pb.cu_seqlens_k).cuda()
         kw["grads"] = (g.make(tuple(t[1].shape), t[1].dtype), g.make(tuple(t[2].shape), t[2].dtype),
                        g.make(tuple(t[3].shape), t[3].dtype))
-        dq, dk, dv = api.flash_attn_varlen_bwd(*t, lse_d, cq, ck, pb.seqlen_q, pb.seqlen_k, **kw)
+        mask = None if pb.attn_mask is None else to_dev(pb.attn_mask, pb.is_bf16)
+        dq, dk, dv = api.flash_attn_varlen_bwd(*t, lse_d, cq, ck, pb.seqlen_q, pb.seqlen_k, attn_mask=mask, **kw)
     else:
         shp_q = (pb.batch, pb.seqlen_q, pb.num_heads, pb.head_size)
         shp_k = (pb.batch, pb.seqlen_k, pb.num_heads_k, pb.head_size)

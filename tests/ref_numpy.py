@@ -12,10 +12,13 @@ W0, W1 = 0x9E3779B9, 0xBB67AE85
 MASK32 = 0xFFFFFFFF
 
 
-def philox4x32_10(ctr, key):
+ROUNDS = 7          # csrc/philox_spec.h (restated here, not imported: this file is independent of it)
+
+
+def philox4x32(ctr, key, rounds=ROUNDS):
     c0, c1, c2, c3 = (int(x) for x in ctr)
     k0, k1 = (int(x) for x in key)
-    for _ in range(10):
+    for _ in range(rounds):
         p0 = M0 * c0
         p1 = M1 * c2
         c0, c1, c2, c3 = ((p1 >> 32) ^ c1 ^ k0) & MASK32, p1 & MASK32, \
@@ -25,13 +28,13 @@ def philox4x32_10(ctr, key):
     return [c0, c1, c2, c3]
 
 
-def philox4x32_10_vec(c0, c1, c2, c3, k0, k1):
+def philox4x32_vec(c0, c1, c2, c3, k0, k1, rounds=ROUNDS):
     """Vectorised over numpy uint64 arrays holding 32-bit values."""
     c0, c1, c2, c3 = (np.asarray(x, dtype=np.uint64) for x in (c0, c1, c2, c3))
     k0 = np.uint64(k0)
     k1 = np.uint64(k1)
     m = np.uint64(MASK32)
-    for _ in range(10):
+    for _ in range(rounds):
         p0 = np.uint64(M0) * c0
         p1 = np.uint64(M1) * c2
         n0 = ((p1 >> np.uint64(32)) ^ c1 ^ k0) & m
@@ -53,7 +56,7 @@ def keep_mask(seed, offset, p_dropout, bh, sq, sk):
     blks = np.tile(np.arange(nblk, dtype=np.uint64), sq)
     k0 = (seed & MASK32) ^ ((offset >> 32) & MASK32)
     k1 = (seed >> 32) & MASK32
-    w = philox4x32_10_vec(rows, blks, np.full_like(rows, bh), np.full_like(rows, offset & MASK32),
+    w = philox4x32_vec(rows, blks, np.full_like(rows, bh), np.full_like(rows, offset & MASK32),
                           k0, k1)
     by = np.zeros((sq * nblk, 16), dtype=np.uint64)
     for i in range(4):

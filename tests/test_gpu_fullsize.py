@@ -1,4 +1,4 @@
-"""Parity at BASELINE.json's FULL sizes (configs 2 and 3), where the CPU oracle would take minutes:
+"""Parity at BASELINE.json's FULL sizes (configs 2, 3 and 4), where the CPU oracle would take minutes:
   * sampled (batch, head) units of the full-size call against fp32 math on the same device, with the
     dropout mask taken from the oracle's Philox (oracle.dropout_mask) -- north_star tolerances;
   * size-independent properties: causality (later keys cannot change earlier rows, bit for bit),
@@ -46,6 +46,7 @@ def _unit_reference(q, k, v, do, scale, causal, keep, rp):
 
 @pytest.mark.parametrize("cfg", ["c3_fwd_bwd_dropout", "c2_fwd"])
 def test_full_size_sampled_units(cfg):
+    import parity
     from flash_attention_hip_b200 import api
     if cfg == "c3_fwd_bwd_dropout":      # BASELINE.json configs[2]
         b, h, s, d, p_drop, seed, offset, units = 16, 32, 4096, 128, 0.1, 1234, 0, [(0, 0), (7, 13), (15, 31)]
@@ -64,14 +65,17 @@ def test_full_size_sampled_units(cfg):
         if p_drop > 0:
             keep = torch.from_numpy(O.dropout_mask(seed, offset, p_drop, bi * h + hi, s, s).astype(np.bool_)).cuda()
             rp = 1.0 / (1.0 - p_drop)
-        r_out, r_lse, r_dq, r_dk, r_dv = _unit_reference(q[bi, :, hi], k[bi, :, hi], v[bi, :, hi], do[bi, :, hi],
-                                                         scale, True, keep, rp)
-        assert _rel(out[bi, :, hi], r_out) < TOL_REL
-        assert float((lse[bi, hi] - r_lse).abs().max()) < TOL_LSE
+        args = (q[bi, :, hi], k[bi, :, hi], v[bi, :, hi], do[bi, :, hi], scale, True, keep, rp)
+        r_out, r_lse, r_dq, r_dk, r_dv = _unit_reference(*args)
+        l_out, l_dq, l_dk, l_dv = _lowprec_unit(*args)
+        tag = f"fullsize/{cfg}/b{bi}h{hi}"
+        n = lambda t: t.float().cpu().numpy()
+        parity.check(tag, "out", n(out[bi, :, hi]), n(r_out), n(l_out))
+        parity.check_lse(tag, n(lse[bi, hi]), n(r_lse))
         if grads is not None:
-            assert _rel(grads[0][bi, :, hi], r_dq) < TOL_REL
-            assert _rel(grads[1][bi, :, hi], r_dk) < TOL_REL
-            assert _rel(grads[2][bi, :, hi], r_dv) < TOL_REL
+            parity.check(tag, "dq", n(grads[0][bi, :, hi]), n(r_dq), n(l_dq))
+            parity.check(tag, "dk", n(grads[1][bi, :, hi]), n(r_dk), n(l_dk))
+            parity.check(tag, "dv", n(grads[2][bi, :, hi]), n(r_dv), n(l_dv))
 
 
 def test_full_size_properties():
@@ -100,3 +104,76 @@ def test_full_size_properties():
     oe, _, _, _ = api.flash_attn_fwd(q, k, ones, is_causal=True, p_dropout=0.3, seed=5, offset=8)
     assert torch.equal(od, od2) and not torch.equal(od, oe)
     assert abs(float(od[:, 2048:].float().mean()) - 1.0) < 5e-3
+
+
+# ---- BASELINE.json configs[3] exactly as SURVEY.md section 8(d) words it -------------------------------------------
+C4_LENS = [128, 8192, 512, 4096, 1000, 2048, 256, 6000]     # 22232 tokens, includes non-multiples of 128
+C4_H, C4_HK = 32, 8
+
+
+def _lowprec_unit(q, k, v, do, scale, causal, keep, rp):
+    """The same unit in a 16-bit pipeline (scores / P / dS / outputs rounded to bf16 as they are produced):
+    its error against the fp32 unit calibrates the second parity criterion (tests/parity.py)."""
+    bf = torch.bfloat16
+    s = ((q @ k.t()).float() * scale)
+    if causal:
+        sq, sk = s.shape
+        s = s.masked_fill(torch.ones(sq, sk, dtype=torch.bool, device=s.device).triu(1 + sk - sq), float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)
+    p = torch.exp(s - lse[:, None])
+    pd = (p if keep is None else p * keep * rp).to(bf)
+    out = (pd @ v).to(bf)
+    dv = (pd.t() @ do)
+    dp = (do @ v.t()).float()
+    if keep is not None:
+        dp = dp * keep * rp
+    d = (do.float() * out.float()).sum(-1, keepdim=True)
+    ds = (p * (dp - d)).to(bf)
+    return out.float(), (scale * (ds @ k).float()), (scale * (ds.t() @ q).float()), dv.float()
+
+
+@pytest.mark.parametrize("d,causal,p_drop", [(128, True, 0.0), (128, False, 0.0), (64, True, 0.0), (64, False, 0.0),
+                                             (128, True, 0.1), (64, True, 0.1)])
+def test_config4_full_mix_sampled_units(d, causal, p_drop):
+    """All eight lengths, H = 32 / 8 (GQA), D = 64 and 128, causal and not, forward + backward, through the
+    packed entry points.  One kv head per sequence is checked in full: its four query heads against fp32 math
+    on the device (dropout mask from the oracle's Philox), dK / dV against the sum over the group."""
+    import itertools
+    import parity
+    from flash_attention_hip_b200 import api
+    lens = C4_LENS
+    cu = torch.tensor([0] + list(itertools.accumulate(lens)), dtype=torch.int32, device="cuda")
+    total, mx = sum(lens), max(lens)
+    q, do = _rand((total, C4_H, d), 400), _rand((total, C4_H, d), 401)
+    k, v = _rand((total, C4_HK, d), 402), _rand((total, C4_HK, d), 403)
+    seed, offset = 3, 2**33 + 5
+    kw = dict(p_dropout=p_drop, is_causal=causal, seed=seed, offset=offset)
+    out, lse, _, _ = api.flash_attn_varlen_fwd(q, k, v, cu, cu, mx, mx, **kw)
+    assert api.last_path() == api.PATH_TCGEN05
+    dq, dk, dv = api.flash_attn_varlen_bwd(do, q, k, v, out, lse, cu, cu, mx, mx, **kw)
+    assert api.last_path() == api.PATH_TCGEN05
+    scale, group, rp = d ** -0.5, C4_H // C4_HK, 1.0 / (1.0 - p_drop)
+    label = f"c4_full/d{d}_{'causal' if causal else 'full'}_p{p_drop}"
+    for b, n in enumerate(lens):
+        if p_drop > 0 and n > 2048:
+            continue                       # the oracle's mask of an 8192 x 8192 unit is minutes of CPU; five sequences carry it
+        t0 = int(cu[b])
+        hk = (3 * b + 1) % C4_HK           # a different kv head per sequence
+        sl = slice(t0, t0 + n)
+        rdk = torch.zeros((n, d), device="cuda"); rdv = torch.zeros((n, d), device="cuda")
+        ldk = torch.zeros((n, d), device="cuda"); ldv = torch.zeros((n, d), device="cuda")
+        for h in range(hk * group, (hk + 1) * group):
+            keep = None
+            if p_drop > 0:
+                keep = torch.from_numpy(O.dropout_mask(seed, offset, p_drop, b * C4_H + h, n, n).astype(np.bool_)).cuda()
+            args = (q[sl, h], k[sl, hk], v[sl, hk], do[sl, h], scale, causal, keep, rp)
+            r_out, r_lse, r_dq, r_dk, r_dv = _unit_reference(*args)
+            l_out, l_dq, l_dk, l_dv = _lowprec_unit(*args)
+            tag = f"{label}/seq{b}(n={n})/h{h}"
+            parity.check(tag, "out", out[sl, h].float().cpu().numpy(), r_out.cpu().numpy(), l_out.cpu().numpy())
+            parity.check_lse(tag, lse[b, h, :n].cpu().numpy(), r_lse.cpu().numpy())
+            parity.check(tag, "dq", dq[sl, h].float().cpu().numpy(), r_dq.cpu().numpy(), l_dq.cpu().numpy())
+            rdk += r_dk; rdv += r_dv; ldk += l_dk; ldv += l_dv
+        tag = f"{label}/seq{b}(n={n})/hk{hk}"
+        parity.check(tag, "dk", dk[sl, hk].float().cpu().numpy(), rdk.cpu().numpy(), ldk.bfloat16().float().cpu().numpy())
+        parity.check(tag, "dv", dv[sl, hk].float().cpu().numpy(), rdv.cpu().numpy(), ldv.bfloat16().float().cpu().numpy())

@@ -1,6 +1,6 @@
 """HostPipelinedAttention (host buffers, batch chunks on three streams) returns bit for bit what one
 unchunked call on device tensors returns, dropout included (the chunks keep their global batch index
-through set_batch_base)."""
+through the batch_base argument of the flash_attn_b200_*_shard entry points)."""
 import pytest
 import torch
 
@@ -23,12 +23,9 @@ def test_pipelined_host_call_equals_one_shot(b, chunks, hk, p_drop):
     assert pipe.launches > 0
 
     q, k, v, do = (t.cuda() for t in (hq, hkk, hv, hdo))
-    api.set_batch_base(base)
-    try:
-        out, lse, _, _ = api.flash_attn_fwd(q, k, v, p_dropout=p_drop, is_causal=True, seed=3, offset=5)
-        dq, dk, dv = api.flash_attn_bwd(do, q, k, v, out, lse, p_dropout=p_drop, is_causal=True, seed=3, offset=5)
-    finally:
-        api.set_batch_base(0)
+    kw = dict(p_dropout=p_drop, is_causal=True, seed=3, offset=5, batch_base=base)
+    out, lse, _, _ = api.flash_attn_fwd(q, k, v, **kw)
+    dq, dk, dv = api.flash_attn_bwd(do, q, k, v, out, lse, **kw)
     assert torch.equal(outs[0], out.cpu())
     # dQ is a sum of fp32 reduce-adds whose order is not fixed run to run: compare with a tolerance
     for got, ref in ((outs[1], dq), (outs[2], dk), (outs[3], dv)):

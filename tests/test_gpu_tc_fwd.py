@@ -62,24 +62,18 @@ CASES = {
 }
 
 
-def run_and_check(pb, seed=42, std=1.0):
+def run_and_check(label, pb, seed=42, std=1.0):
     import gpu_util as G
     q, k, v, _ = cases.make_inputs(pb, seed=seed, with_dout=False, std=std)
-    ref = O.forward(pb, q, k, v)
+    ref, lp_out = G.oracle_fwd(pb, q, k, v)
     got = G.run_fwd(pb, q, k, v)
     assert got["path"] == 2, "tcgen05 path did not run"
-    err = cases.rel_err(G.f32(got["out"], pb), ref["out_f32"])
-    assert err < TOL_REL, f"out rel err {err}"
-    assert np.array_equal(np.isposinf(got["lse"]), np.isposinf(ref["lse"]))
-    fin = np.isfinite(ref["lse"])
-    lerr = np.abs(got["lse"][fin] - ref["lse"][fin]).max(initial=0)
-    assert lerr < TOL_LSE, f"lse err {lerr}"
-    return err, lerr
+    G.check_fwd(label, pb, got, ref, lp_out)
 
 
 @pytest.mark.parametrize("name", list(CASES))
 def test_tc_fwd(name):
-    run_and_check(CASES[name]())
+    run_and_check("tc_fwd/" + name, CASES[name]())
 
 
 def test_tc_fwd_growing_max_forces_rescale():

@@ -43,29 +43,60 @@ def test_tc_attn_mask_fwd_bwd(name):
     pb = mk()
     pb.attn_mask = _mask(pb, mb, mh, seed=21, pad_from=pad, neg=neg)
     q, k, v, dout = cases.make_inputs(pb, seed=13)
-    ref = O.forward(pb, q, k, v)
+    ref, lp_out = G.oracle_fwd(pb, q, k, v)
     got = G.run_fwd(pb, q, k, v)
     assert got["path"] == 2, "tcgen05 forward did not run"
-    assert cases.rel_err(G.f32(got["out"], pb), ref["out_f32"]) < TOL_REL
-    fin = np.isfinite(ref["lse"])
-    assert np.array_equal(np.isfinite(got["lse"]), fin)
-    assert np.abs(got["lse"][fin] - ref["lse"][fin]).max() < 1e-3
-    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    G.check_fwd("tc_mask/" + name, pb, got, ref, lp_out)
+    rb, lp = G.oracle_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
     gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
     assert gb["path"] == 2, "tcgen05 backward did not run"
-    for t in ("dq", "dk", "dv"):
-        assert cases.rel_err(G.f32(gb[t], pb), rb[t + "_f32"]) < TOL_REL, t
+    G.check_bwd("tc_mask/" + name, pb, gb, rb, lp)
 
 
-def test_tc_mask_fully_masked_rows_give_zero_and_inf_lse():
+@pytest.mark.parametrize("is_bf16", [True, False])
+@pytest.mark.parametrize("d,sk", [(128, 128), (64, 128), (64, 2048), (128, 2048), (64, 1600)])
+def test_tc_mask_fully_masked_rows_give_zero_and_inf_lse(d, sk, is_bf16):
+    """include/flash_attn.h: a row whose bias is all -inf gives out = 0 and LSE = +inf -- for every head size and
+    key length (the D = 64 builds compute part of the exponentials on the FMA pipe from 1536 keys up, where a
+    clamped polynomial would turn exp2(-inf) into 2^-125; masked builds must not use it)."""
     import gpu_util as G
-    pb = cases.dense(1, 128, 128, 2, 2, 128)
-    m = np.zeros((1, 1, 128, 128), np.float32)
+    pb = cases.dense(1, 128, sk, 2, 2, d, is_bf16=is_bf16)
+    m = np.zeros((1, 1, 128, sk), np.float32)
     m[:, :, 5:9, :] = -np.inf                    # four query rows see nothing
-    pb.attn_mask = O.to_storage(m, True)
+    m[:, :, 40:50, sk // 2:] = -np.inf           # and ten see only the first half
+    pb.attn_mask = O.to_storage(m, is_bf16)
     q, k, v, _ = cases.make_inputs(pb, seed=3, with_dout=False)
+    ref, lp_out = G.oracle_fwd(pb, q, k, v)
     got = G.run_fwd(pb, q, k, v)
-    out = G.f32(got["out"], pb).reshape(128, 2, 128)
+    out = G.f32(got["out"], pb).reshape(128, 2, d)
     assert got["path"] == 2
     assert np.all(out[5:9] == 0) and np.all(np.isposinf(got["lse"][0, :, 5:9]))
     assert np.all(np.isfinite(got["lse"][0, :, :5]))
+    G.check_fwd(f"tc_mask/fully_masked_d{d}_sk{sk}_{'bf16' if is_bf16 else 'fp16'}", pb, got, ref, lp_out)
+
+
+@pytest.mark.parametrize("causal,sq,sk", [(False, 256, 2048), (True, 2048, 1664)])
+def test_tc_mask_minus_inf_key_padding_d64_long(causal, sq, sk):
+    """-inf key padding at D = 64 with >= 1536 keys (the FMA-pipe exp2 switch), dense causal with sq > sk too:
+    some query rows end up with no visible key at all."""
+    import gpu_util as G
+    pb = cases.dense(2, sq, sk, 4, 2, 64, is_causal=causal)
+    rng = np.random.default_rng(5)
+    m = rng.standard_normal((2, 1, sq, sk), dtype=np.float32)
+    m[0, :, :, sk - 300:] = -np.inf              # batch 0: the last 300 keys are padding
+    m[1, :, :, :sk - 100] = -np.inf              # batch 1: only the last 100 keys are real
+    pb.attn_mask = O.to_storage(m, True)
+    q, k, v, dout = cases.make_inputs(pb, seed=4)
+    ref, lp_out = G.oracle_fwd(pb, q, k, v)
+    got = G.run_fwd(pb, q, k, v)
+    assert got["path"] == 2
+    G.check_fwd(f"tc_mask/minus_inf_padding_d64_{'causal' if causal else 'full'}", pb, got, ref, lp_out)
+    dead = np.isposinf(ref["lse"])
+    if causal:
+        assert dead.any()                        # rows above the bottom-right aligned diagonal of batch 0's real keys
+    outf = G.f32(got["out"], pb).reshape(2, sq, 4, 64)
+    assert np.all(outf.transpose(0, 2, 1, 3)[dead] == 0)
+    rb, lp = G.oracle_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
+    gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
+    assert gb["path"] == 2
+    G.check_bwd(f"tc_mask/minus_inf_padding_d64_{'causal' if causal else 'full'}", pb, gb, rb, lp)

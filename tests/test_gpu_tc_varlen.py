@@ -45,17 +45,21 @@ def test_tc_varlen_fwd_bwd(name):
     import gpu_util as G
     pb = CASES[name]()
     q, k, v, dout = cases.make_inputs(pb, seed=11)
-    ref = O.forward(pb, q, k, v)
+    big = pb.total_q > 8000            # the C4 mixes: one oracle pass is enough CPU time
+    if big:
+        ref, lp_out = O.forward(pb, q, k, v), None
+    else:
+        ref, lp_out = G.oracle_fwd(pb, q, k, v)
     got = G.run_fwd(pb, q, k, v)
     assert got["path"] == 2, "tcgen05 forward did not run"
-    assert cases.rel_err(G.f32(got["out"], pb), ref["out_f32"]) < TOL_REL
-    check_lse(got["lse"], ref["lse"], pb)
-    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    G.check_fwd("tc_varlen/" + name, pb, got, ref, lp_out)
+    if big:
+        rb, lp = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"]), None
+    else:
+        rb, lp = G.oracle_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
     gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
     assert gb["path"] == 2, "tcgen05 backward did not run"
-    for t in ("dq", "dk", "dv"):
-        err = cases.rel_err(G.f32(gb[t], pb), rb[t + "_f32"])
-        assert err < TOL_REL, f"{t} rel err {err}"
+    G.check_bwd("tc_varlen/" + name, pb, gb, rb, lp)
 
 
 def test_varlen_equals_dense_per_sequence():

@@ -1,8 +1,8 @@
 """CPU-only: pins the oracle (oracle/attn_oracle.c).
 
 The reference has no fixtures for this path, so the
-oracle is pinned by (1) the published Random123 Philox4x32-10 known-answer
-vectors, (2) agreement of its fp32 build with its fp64 build and with an
+oracle is pinned by (1) the published Random123 Philox4x32 known-answer
+vectors for 7 rounds (the dropout specification, csrc/philox_spec.h) and 10 rounds, (2) agreement of its fp32 build with its fp64 build and with an
 independent numpy float64 restatement, (3) finite differences, and
 (4) committed golden outputs under tests/golden/.
 """
@@ -17,19 +17,28 @@ from oracle import oracle as O
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 
-# Random123 kat_vectors, philox4x32 10 rounds: (counter, key, expected)
+# Random123 kat_vectors, philox4x32 with 7 and 10 rounds: (rounds, counter, key, expected)
+_PI_CTR, _PI_KEY = [0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0]
 PHILOX_KAT = [
-    ([0, 0, 0, 0], [0, 0], [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]),
-    ([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]),
-    ([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0],
-     [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]),
+    (7, [0, 0, 0, 0], [0, 0], [0x5F6FB709, 0x0D893F64, 0x4F121F81, 0x4F730A48]),
+    (7, [0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x5207DDC2, 0x45165E59, 0x4D8EE751, 0x8C52F662]),
+    (7, _PI_CTR, _PI_KEY, [0x4DFCCABA, 0x190A87F0, 0xC47362BA, 0xB6B5242A]),
+    (10, [0, 0, 0, 0], [0, 0], [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]),
+    (10, [0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]),
+    (10, _PI_CTR, _PI_KEY, [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]),
 ]
 
 
-@pytest.mark.parametrize("ctr,key,exp", PHILOX_KAT)
-def test_philox_known_answers(ctr, key, exp):
-    assert list(O.philox(ctr, key)) == exp
-    assert R.philox4x32_10(ctr, key) == exp
+@pytest.mark.parametrize("rounds,ctr,key,exp", PHILOX_KAT)
+def test_philox_known_answers(rounds, ctr, key, exp):
+    assert list(O.philox(ctr, key, rounds)) == exp
+    assert R.philox4x32(ctr, key, rounds) == exp
+    if rounds == O.philox_rounds():          # the generator the dropout specification uses
+        assert list(O.philox(ctr, key)) == exp
+
+
+def test_dropout_spec_round_count():
+    assert O.philox_rounds() == 7 == R.ROUNDS
 
 
 def test_storage_roundtrip_matches_numpy_half():
