@@ -33,16 +33,6 @@ namespace {
 constexpr int kTileM = 128;        // query rows per tile (= TMEM lanes)
 constexpr int kTileN = 128;        // keys per KV tile
 constexpr int kThreads = 384;
-#ifndef FA_FWD_DRAW_WG
-#define FA_FWD_DRAW_WG 0
-#endif
-// Dropout builds: a fourth warpgroup (warps 12-15) draws the Philox keep bits and hands them to the softmax warps
-// through shared memory as packed bit masks (16 bytes per row and KV tile), so that the softmax warps carry the
-// non-dropout instruction stream plus one PRMT + AND per pair.  0 = the softmax warps draw their own bits under
-// the MUFU stream (round 1).
-constexpr bool kDrawWGBuild = FA_FWD_DRAW_WG != 0;
-constexpr int kDrawWarp0 = 12;
-constexpr int threads_for(bool dropout) { return (dropout && kDrawWGBuild) ? 512 : kThreads; }
 constexpr int kMmaWarp = 8, kLoadWarp = 9;
 constexpr uint32_t kPOff = 32;     // P's first column inside its S tile
 constexpr float kRescaleThreshold = 8.0f;  // in log2 units
@@ -86,19 +76,13 @@ struct Cfg {
   static constexpr uint32_t kSmemK = kQTiles * kTileBytes;
   static constexpr uint32_t kSmemV = kSmemK + kStages * kTileBytes;
   static constexpr uint32_t kSmemBar = kSmemV + kStages * kTileBytes;
-  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8 + 7 + 8;   // + bits_full / bits_empty [2 tiles][2 stages]
+  static constexpr uint32_t kNumBars = 1 + 4 * kStages + 8 + 7;
   static constexpr uint32_t kSmemDesc = kSmemBar + 512;       // 3 x 128 B tensor-map staging (packed inputs)
   static constexpr uint32_t kSmemO = kSmemDesc + 3 * 128;     // epilogue staging: 4 KB (32 rows x 64 columns) per softmax warp
   static constexpr uint32_t kSmemBytesNoStage = kSmemO + 1024;                // + alignment slack
-  // keep-bit masks of the draw warpgroup: [2 tiles][2 stages][128 rows][16 B] (dropout builds with FA_FWD_DRAW_WG; they
-  // have no epilogue staging, so the block sits where that would start)
-  static constexpr uint32_t kSmemBits = kSmemO;
-  static constexpr uint32_t kSmemBytesDraw = kSmemBits + 4 * 2048 + 1024;
   static constexpr uint32_t kSmemBytes = kSmemO + kQTiles * 4 * 4096 + 1024;
   static_assert(kSmemBytes <= 232448, "over the 227 KB a CTA may ask for");
-  static constexpr uint32_t smem_bytes(bool stage_o, bool draw_wg = false) {
-    return stage_o ? kSmemBytes : draw_wg ? kSmemBytesDraw : kSmemBytesNoStage;
-  }
+  static constexpr uint32_t smem_bytes(bool stage_o) { return stage_o ? kSmemBytes : kSmemBytesNoStage; }
   static_assert(kNumBars * 8 + 16 <= 512, "barrier block (+ tmem slot, item queue) overflows");
   static_assert(kSmemBytesNoStage > 116 * 1024, "one CTA per SM is what makes the per-SM tensor-map slots private");
 };
@@ -122,7 +106,6 @@ __device__ ptx::TensorMapSlot g_fwd_slots[ptx::kMaxSm][2][3];   // two sets: the
 struct Bars {
   uint32_t q_full, k_full, k_empty, v_full, v_empty, s_full, p_lo, p_hi, pv_done;  // first of each group
   uint32_t q_empty, o_free /*[2]*/, sched_full /*[2]*/, sched_empty /*[2]*/;
-  uint32_t bits_full /*[2 tiles][2 stages]*/, bits_empty /*[2][2]*/;
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -196,13 +179,11 @@ struct Item {
 };
 
 template <int D, bool kBF16, bool kDropout, bool kMask>
-__global__ void __launch_bounds__(threads_for(kDropout), 1)
+__global__ void __launch_bounds__(kThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const TcFwdArgs a) {
   using C = Cfg<D>;
   constexpr bool kStageO = stage_o(kDropout);
-  constexpr bool kDrawWG = kDropout && kDrawWGBuild;
-  static_assert(!(kDrawWG && kStageO), "the keep-bit block takes the place of the epilogue staging");
   constexpr bool kMaskStage = kMask && kStageO;       // the bias tile borrows the epilogue's staging blocks
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -264,8 +245,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   B.o_free = B.q_empty + 8;
   B.sched_full = B.o_free + 16;
   B.sched_empty = B.sched_full + 16;
-  B.bits_full = B.sched_empty + 16;
-  B.bits_empty = B.bits_full + 32;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(sgen + C::kSmemBar + C::kNumBars * 8);
   volatile int *sched_item = reinterpret_cast<volatile int *>(tmem_slot + 2);   // [2]
   constexpr int kSoftmaxThreads = C::kQTiles * kTileM;
@@ -286,11 +265,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       ptx::mbar_init(B.pv_done + 8 * t, 1);
       ptx::mbar_init(B.o_free + 8 * t, kTileM);
       ptx::mbar_init(B.sched_full + 8 * t, 1);
-      ptx::mbar_init(B.sched_empty + 8 * t, 1 + kSoftmaxThreads + (kDrawWG ? 128 : 0));   // MMA lane + every softmax (and draw) thread
-      for (int st = 0; st < 2; ++st) {
-        ptx::mbar_init(B.bits_full + 8 * (2 * t + st), 128);         // the draw warpgroup's threads
-        ptx::mbar_init(B.bits_empty + 8 * (2 * t + st), kTileM);     // the tile's softmax threads
-      }
+      ptx::mbar_init(B.sched_empty + 8 * t, 1 + kSoftmaxThreads);   // MMA lane + every softmax thread
     }
     ptx::fence_mbar_init();
   }
@@ -319,65 +294,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     return L;
   };
 
-  if (warp >= kDrawWarp0) {
-    // ======================= draw warpgroup (dropout builds with FA_FWD_DRAW_WG) =======================
-    // Thread r draws the keep bits of rows r of BOTH query tiles, one KV tile at a time, in the order the
-    // softmax warps consume them (csrc/philox_spec.h: one Philox call per 16 columns, one byte per column).
-    // Hand-over format, 16 bytes per row and KV tile: word u covers columns [32u, 32u + 32); bit wd of byte
-    // `by` = keep(column 32u + 4 wd + by), bit 4 + wd = keep(column 32u + 16 + 4 wd + by) -- i.e. Philox word wd
-    // of the first / second call of the pair, byte by -- so that `word << (7 - bit)` puts the verdicts of two
-    // adjacent columns at the top of two adjacent bytes, where PRMT's sign-replicate mode picks them up.
-    if constexpr (kDrawWG) {
-      ptx::setmaxnreg_dec<72>();
-      const int r_in_tile = (warp & 3) * 32 + lane;
-      DropConst dc;
-      dc.add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
-      dc.t_msb = a.drop_threshold >= 128u;
-      int cnt[2] = {0, 0};                              // KV tiles drawn so far per query tile (ring stage / phase)
-      for (int n = 0;; ++n) {
-        const int L = next_item(n);
-        if (L < 0) break;
-        const Item it = decode(L);
-        if (!it.valid) continue;
-        const uint32_t bh = (uint32_t)((a.batch_base + it.bidx) * a.h + it.head);
-        for (int j = 0; j < it.nmax; ++j) {
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            if (j >= it.ntile[t]) continue;
-            const int c = cnt[t] + j, st = c & 1;
-            if (c >= 2) ptx::mbar_wait(B.bits_empty + 8 * (2 * t + st), ((c >> 1) - 1) & 1);
-            const uint32_t row = (uint32_t)(it.m0 + t * kTileM + r_in_tile);
-            uint32_t V[4];
-#pragma unroll
-            for (int up = 0; up < 2; ++up) {            // two words (four calls = four independent chains) at a time
-              uint32_t pc[4][4];
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                pc[q][0] = row; pc[q][1] = (uint32_t)(j * (kTileN / 16) + up * 4 + q); pc[q][2] = bh; pc[q][3] = a.ctr3;
-              }
-#pragma unroll
-              for (int r = 0; r < FA_PHILOX_ROUNDS; ++r)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) fa_philox_round(pc[q], a.key0, a.key1, r);
-#pragma unroll
-              for (int w2 = 0; w2 < 2; ++w2) {
-                uint32_t v = 0;
-#pragma unroll
-                for (int wd = 0; wd < 4; ++wd) {
-                  v |= (keep_word(pc[2 * w2][wd], dc) >> (7 - wd)) & (0x01010101u << wd);
-                  v |= (keep_word(pc[2 * w2 + 1][wd], dc) >> (3 - wd)) & (0x01010101u << (4 + wd));
-                }
-                V[2 * up + w2] = v;
-              }
-            }
-            st_shared_v4(sbase + C::kSmemBits + (uint32_t)(2 * t + st) * 2048u + (uint32_t)r_in_tile * 16u, V[0], V[1], V[2], V[3]);
-            ptx::mbar_arrive(B.bits_full + 8 * (2 * t + st));
-          }
-        }
-        cnt[0] += it.ntile[0]; cnt[1] += it.ntile[1];
-      }
-    }
-  } else if (warp >= 8) {
+  if (warp >= 8) {
     // ======================= producer warpgroup ================================
     ptx::setmaxnreg_dec<40>();
     if (warp == kLoadWarp) {
@@ -544,7 +461,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::setmaxnreg_dec<40>();                        // D = 256: the second softmax warpgroup has no tile
   } else {
     // ======================= softmax warpgroups ===================================
-    ptx::setmaxnreg_inc<kDrawWG ? 200 : 232>();        // 16 warps: 8 x 200 + 4 x 40 + 4 x 72 = 2048 per lane
+    ptx::setmaxnreg_inc<232>();
     const int t = warp >> 2;                          // query tile of this warpgroup
     const int r_in_tile = (warp & 3) * 32 + lane;     // TMEM lane == row inside the tile
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
@@ -587,13 +504,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     // exponentiated, the loop steps the four Philox calls of the half that is handed over next -- (j, 1)
     // during half 0, (j + 1, 0) during half 1 -- five rounds per 8 exponentials, round-robin over the
     // calls (four independent chains).  keepw[16 h + w]: bit 7 of each byte = keep, half h of the tile.
-    constexpr bool kOwnDraw = kDropout && !kDrawWG;     // the softmax warps draw their own keep bits (round-1 scheme)
-    uint32_t keepw[kOwnDraw ? 32 : 1];
+    uint32_t keepw[kDropout ? 32 : 1];
     uint32_t pc[4][4];
     auto ctr_init = [&](int q, int j, int hf) {
       pc[q][0] = (uint32_t)row; pc[q][1] = (uint32_t)(j * (kTileN / 16) + hf * 4 + q); pc[q][2] = bh; pc[q][3] = a.ctr3;
     };
-    if constexpr (kOwnDraw) {
+    if constexpr (kDropout) {
       FA_TRACE_EV(trs, 17);
       if (n_t > 0) {                      // the item's first half: whole calls, before S arrives
 #pragma unroll
@@ -634,13 +550,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             st_shared_v4(mstage + r * 128 + ((ch ^ (r & 7)) << 4), m0v[i].x, m0v[i].y, m0v[i].z, m0v[i].w);
           }
         }
-      }
-      uint4 kb4 = make_uint4(0, 0, 0, 0);                 // draw warpgroup: this row's 128 keep bits of KV tile j
-      if constexpr (kDrawWG) {
-        const int c = cnt + j, st = c & 1;
-        ptx::mbar_wait(B.bits_full + 8 * (2 * t + st), (c >> 1) & 1);
-        kb4 = ld_shared_v4(sbase + C::kSmemBits + (uint32_t)(2 * t + st) * 2048u + (uint32_t)r_in_tile * 16u);
-        ptx::mbar_arrive(B.bits_empty + 8 * (2 * t + st));
       }
       FA_TRACE_EV(trs, 10);
       ptx::mbar_wait(B.s_full + 8 * t, (cnt + j) & 1);
@@ -736,26 +645,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
           m_run = m_new;
           ptx::mbar_wait(B.pv_done + 8 * t, (cnt + j - 1) & 1);   // O_t holds tiles 0..j-1
           ptx::tc_fence_after();
-          if constexpr (kDrawWG) {           // 200 registers: 16-column chunks keep the whole S row live across this (rare) path
-#pragma unroll 1
-            for (int c = 0; c < D / 16; ++c) {
-              uint32_t o[16];
-              ptx::tmem_ld_x16(tO + c * 16, o);
-              ptx::tmem_wait_ld();
 #pragma unroll
-              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-              ptx::tmem_st_x16(tO + c * 16, o);
-            }
-          } else {
+          for (int c = 0; c < D / 32; ++c) {
+            uint32_t o[32];
+            ptx::tmem_ld_x32(tO + c * 32, o);
+            ptx::tmem_wait_ld();
 #pragma unroll
-            for (int c = 0; c < D / 32; ++c) {
-              uint32_t o[32];
-              ptx::tmem_ld_x32(tO + c * 32, o);
-              ptx::tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-              ptx::tmem_st_x32(tO + c * 32, o);
-            }
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            ptx::tmem_st_x32(tO + c * 32, o);
           }
           ptx::tmem_wait_st();
         }
@@ -786,20 +683,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             else l01 = __fadd2_rn(l01, x);
             s[c / 2] = pack_pair(x.x, x.y, kBF16);
           }
-          if constexpr (kDrawWG) {
-            // this group's 8 columns 64 half + 8 g .. + 7: word u = 2 half + g / 4, call parity (g / 2) % 2,
-            // Philox words wd = 2 (g % 2) and wd + 1; two pairs (bytes 0-1, 2-3) per Philox word
-            const uint32_t kw = (2 * half + g / 4) == 0 ? kb4.x : (2 * half + g / 4) == 1 ? kb4.y : (2 * half + g / 4) == 2 ? kb4.z : kb4.w;
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int bit = 4 * ((g / 2) % 2) + 2 * (g % 2) + u;
-              uint32_t m01, m23;
-              expand_keep(kw << (7 - bit), m01, m23);
-              s[half * 32 + 4 * g + 2 * u] &= m01;
-              s[half * 32 + 4 * g + 2 * u + 1] &= m23;
-            }
-          }
-          if constexpr (kOwnDraw) {
+          if constexpr (kDropout) {
             if (kApplyInGroup) {            // this group's 8 entries: keep words 2g, 2g + 1 of the current half
 #pragma unroll
               for (int u = 0; u < 2; ++u) {
@@ -824,7 +708,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       };
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
-        if constexpr (kOwnDraw) {
+        if constexpr (kDropout) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) ctr_init(q, half ? j + 1 : j, 1 - half);
         }
@@ -835,7 +719,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         constexpr int kEmu = kMask ? 0 : (kEmuPer8 == 0 && D == 64 && !kDropout) ? 4 : kEmuPer8;   // a bias may hold -inf: ex2_poly2 would give 2^-125, not 0
         if (kEmu == 0 || need_mask || !a.use_emu) exp_half(std::integral_constant<int, 0>{}, half);
         else exp_half(std::integral_constant<int, kEmu>{}, half);
-        if constexpr (kOwnDraw) {
+        if constexpr (kDropout) {
           if (!kApplyInGroup) {
 #pragma unroll
             for (int w = half * 16; w < half * 16 + 16; ++w) {
@@ -1042,8 +926,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   int dev = 0, sm_count = 0;
   if ((e = current_device(&dev, &sm_count))) return e;
   static std::atomic<uint64_t> smem_opt_in{0};   // per instantiation, one bit per device
-  constexpr bool kDraw = kDropout && kDrawWGBuild;
-  if ((e = ensure_dynamic_smem(kern, (int)C::smem_bytes(stage_o(kDropout), kDraw), dev, smem_opt_in))) return e;
+  if ((e = ensure_dynamic_smem(kern, (int)C::smem_bytes(stage_o(kDropout)), dev, smem_opt_in))) return e;
   a.nqb = (sq_eff + C::kQTiles * kTileM - 1) / (C::kQTiles * kTileM);
   a.n_items = a.nqb * h_eff * p.b;
   // no more items than SMs: one item per CTA, no counter
@@ -1054,7 +937,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
     grid = sm_count;
     if ((e = take_sched_slot(g_fwd_sched, dev, g_fwd_sched_addr, g_fwd_ticket, &a.sched))) return e;
   }
-  kern<<<grid, threads_for(kDropout), C::smem_bytes(stage_o(kDropout), kDraw), stream>>>(tq, tk, tv, a);
+  kern<<<grid, kThreads, C::smem_bytes(stage_o(kDropout)), stream>>>(tq, tk, tv, a);
   const cudaError_t err = cudaGetLastError();
   return err == cudaSuccess ? nullptr : cudaGetErrorString(err);
 }

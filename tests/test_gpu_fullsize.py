@@ -24,8 +24,10 @@ def _rel(a, ref):
     return float((a.float() - ref).abs().max() / ref.abs().max())
 
 
-def _unit_reference(q, k, v, do, scale, causal, keep, rp):
-    """fp32 attention forward + backward of ONE (batch, head) unit; keep: bool [sq, sk] or None."""
+def _unit_reference(q, k, v, do, scale, causal, keep, rp, out_given=None):
+    """fp32 attention forward + backward of ONE (batch, head) unit; keep: bool [sq, sk] or None.
+    out_given: the `out` tensor the backward entry point was handed (reference flash_attn.h:72): softmax_d =
+    rowsum(dO o out) is defined on THAT tensor (16-bit), not on an unrounded recomputation."""
     q, k, v, do = (t.float() for t in (q, k, v, do))
     s = (q @ k.t()) * scale
     if causal:
@@ -39,7 +41,7 @@ def _unit_reference(q, k, v, do, scale, causal, keep, rp):
     dp = do @ v.t()
     if keep is not None:
         dp = dp * keep * rp
-    d = (do * out).sum(-1, keepdim=True)
+    d = (do * (out if out_given is None else out_given.float())).sum(-1, keepdim=True)
     ds = p * (dp - d)
     return out, lse, scale * (ds @ k), scale * (ds.t() @ q), dv
 
@@ -65,7 +67,7 @@ def test_full_size_sampled_units(cfg):
         if p_drop > 0:
             keep = torch.from_numpy(O.dropout_mask(seed, offset, p_drop, bi * h + hi, s, s).astype(np.bool_)).cuda()
             rp = 1.0 / (1.0 - p_drop)
-        args = (q[bi, :, hi], k[bi, :, hi], v[bi, :, hi], do[bi, :, hi], scale, True, keep, rp)
+        args = (q[bi, :, hi], k[bi, :, hi], v[bi, :, hi], do[bi, :, hi], scale, True, keep, rp, out[bi, :, hi])
         r_out, r_lse, r_dq, r_dk, r_dv = _unit_reference(*args)
         l_out, l_dq, l_dk, l_dv = _lowprec_unit(*args)
         tag = f"fullsize/{cfg}/b{bi}h{hi}"
@@ -111,7 +113,7 @@ C4_LENS = [128, 8192, 512, 4096, 1000, 2048, 256, 6000]     # 22232 tokens, incl
 C4_H, C4_HK = 32, 8
 
 
-def _lowprec_unit(q, k, v, do, scale, causal, keep, rp):
+def _lowprec_unit(q, k, v, do, scale, causal, keep, rp, out_given=None):
     """The same unit in a 16-bit pipeline (scores / P / dS / outputs rounded to bf16 as they are produced):
     its error against the fp32 unit calibrates the second parity criterion (tests/parity.py)."""
     bf = torch.bfloat16
@@ -127,7 +129,7 @@ def _lowprec_unit(q, k, v, do, scale, causal, keep, rp):
     dp = (do @ v.t()).float()
     if keep is not None:
         dp = dp * keep * rp
-    d = (do.float() * out.float()).sum(-1, keepdim=True)
+    d = (do.float() * (out if out_given is None else out_given).float()).sum(-1, keepdim=True)
     ds = (p * (dp - d)).to(bf)
     return out.float(), (scale * (ds @ k).float()), (scale * (ds.t() @ q).float()), dv.float()
 
@@ -166,7 +168,7 @@ def test_config4_full_mix_sampled_units(d, causal, p_drop):
             keep = None
             if p_drop > 0:
                 keep = torch.from_numpy(O.dropout_mask(seed, offset, p_drop, b * C4_H + h, n, n).astype(np.bool_)).cuda()
-            args = (q[sl, h], k[sl, hk], v[sl, hk], do[sl, h], scale, causal, keep, rp)
+            args = (q[sl, h], k[sl, hk], v[sl, hk], do[sl, h], scale, causal, keep, rp, out[sl, h])
             r_out, r_lse, r_dq, r_dk, r_dv = _unit_reference(*args)
             l_out, l_dq, l_dk, l_dv = _lowprec_unit(*args)
             tag = f"{label}/seq{b}(n={n})/h{h}"
