@@ -278,3 +278,29 @@ def cp_store(dst: torch.Tensor, src: torch.Tensor, stream: Optional[torch.cuda.S
     fn = _ext("flash_attn_b200_cp_store", [_vp, _vp, _i64, _b, _vp])
     _check(fn(_ptr(dst), _ptr(src), src.numel(), dst.dtype == torch.bfloat16, _stream_ptr(stream)),
            "flash_attn_b200_cp_store")
+
+
+STATIC_SCRATCH_BYTES = 32 << 20   # FA_B200_STATIC_SCRATCH_BYTES (include/flash_attn_b200_ext.h)
+
+
+def flash_attn_bwd_static_scratch(dout, q, k, v, out, softmax_lse, *, p_dropout: float = 0.0,
+                                  softmax_scale: Optional[float] = None, is_causal: bool = False,
+                                  seed: int = 0, offset: int = 0,
+                                  grads: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None,
+                                  stream: Optional[torch.cuda.Stream] = None):
+    """Dense backward through `flash_attn_b200_bwd_static_scratch`: the library's own static device array is the
+    scratch, the call allocates nothing (pass `grads` to keep torch from allocating the outputs either).
+    Raises FlashAttnError when the problem needs more than STATIC_SCRATCH_BYTES."""
+    for t in (dout, q, k, v, out):
+        assert t.is_cuda and t.is_contiguous()
+    b, sq, h, d = q.shape
+    _, sk, hk, _ = k.shape
+    scale = float(d) ** -0.5 if softmax_scale is None else float(softmax_scale)
+    dq, dk, dv = grads if grads is not None else (torch.empty_like(q), torch.empty_like(k), torch.empty_like(v))
+    fn = _ext("flash_attn_b200_bwd_static_scratch",
+              [_vp] * 9 + [_i] * 6 + [_f, _f, _b, _b, _vp, _u64, _u64])
+    ok = fn(_ptr(dout), _ptr(q), _ptr(k), _ptr(v), _ptr(out), _ptr(softmax_lse), _ptr(dq), _ptr(dk), _ptr(dv),
+            b, sq, sk, h, hk, d, p_dropout, scale, is_causal, q.dtype == torch.bfloat16, _stream_ptr(stream),
+            seed, offset)
+    _check(ok, "flash_attn_b200_bwd_static_scratch")
+    return dq, dk, dv

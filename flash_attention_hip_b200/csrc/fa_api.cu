@@ -358,6 +358,60 @@ bool flash_attn_b200_varlen_bwd_shard(int batch_base, const void *dout, const vo
   }
 }
 
+// ---- backward without any allocation (include/flash_attn_b200_ext.h) ---------------------------------
+// softmax_d and dq_accum, the two scratch tensors flash_attn_bwd takes from its caller, live in ONE file-scope
+// device array of FA_B200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit.  In host
+// code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is fetched once
+// per device with cudaGetSymbolAddress (that device current) and handed to the kernels as a plain pointer.
+static __device__ __align__(256) float g_static_scratch[FA_B200_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+static const char *static_scratch_base(float **base) {
+  static std::atomic<float *> cache[fa::kMaxCachedDevices];   // zero-initialised; re-fetching is harmless
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return "cudaGetDevice failed";
+  const bool cached = dev >= 0 && dev < fa::kMaxCachedDevices;
+  float *ptr = cached ? cache[dev].load(std::memory_order_acquire) : nullptr;
+  if (!ptr) {
+    if (cudaGetSymbolAddress(reinterpret_cast<void **>(&ptr), g_static_scratch) != cudaSuccess || !ptr)
+      return "cudaGetSymbolAddress(static scratch) failed";
+    if (cached) cache[dev].store(ptr, std::memory_order_release);
+  }
+  *base = ptr;
+  return nullptr;
+}
+
+bool flash_attn_b200_bwd_static_scratch(const void *dout, const void *q, const void *k, const void *v,
+                                        const void *out, const void *softmax_lse, void *dq, void *dk, void *dv,
+                                        int batch_size, int seqlen_q, int seqlen_k, int num_heads, int num_heads_k,
+                                        int head_size, float p_dropout, float softmax_scale, bool is_causal,
+                                        bool is_bf16, fa_stream_t stream, uint64_t seed, uint64_t offset) {
+  const char *fn = "flash_attn_b200_bwd_static_scratch";
+  try {
+    if (batch_size < 0 || seqlen_q < 0 || seqlen_k < 0 || num_heads <= 0 || head_size <= 0)
+      return fail("%s: bad shape", fn);
+    const long long sq_r = (static_cast<long long>(seqlen_q) + 127) / 128 * 128;
+    const long long d_r = (static_cast<long long>(head_size) + 31) / 32 * 32;
+    // softmax_d [b, h, sq_rounded] first (padded to a 256-byte boundary), then dq_accum [b, sq_rounded, h, d_rounded]
+    const long long d_floats = (static_cast<long long>(batch_size) * num_heads * sq_r + 63) / 64 * 64;
+    const long long acc_floats = static_cast<long long>(batch_size) * sq_r * num_heads * d_r;
+    const long long need = (d_floats + acc_floats) * static_cast<long long>(sizeof(float));
+    if (need > static_cast<long long>(FA_B200_STATIC_SCRATCH_BYTES))
+      return fail("%s: this problem needs %lld bytes of scratch (softmax_d + dq_accum = 4*batch*heads*"
+                  "seqlen_q_rounded*(1 + head_size_rounded)), the static array holds %lld: use flash_attn_bwd "
+                  "with caller-owned scratch", fn, need, static_cast<long long>(FA_B200_STATIC_SCRATCH_BYTES));
+    float *base = nullptr;
+    if (const char *e = static_scratch_base(&base)) return fail("%s: %s", fn, e);
+    const Shape s{batch_size, seqlen_q, seqlen_k, static_cast<int>(sq_r), (seqlen_k + 127) / 128 * 128,
+                  num_heads, num_heads_k, head_size, static_cast<int>(d_r)};
+    // num_splits = 0: the ordered-dQ mode keeps its turn counters in a stream-ordered temporary (an allocation)
+    return bwd_impl(fn, dout, q, k, v, out, base, softmax_lse, nullptr, nullptr, false, dq, dk, dv,
+                    base + d_floats, s, p_dropout, softmax_scale, is_causal, is_bf16, /*num_splits=*/0, stream,
+                    seed, offset, nullptr, nullptr);
+  } catch (...) {
+    return fail("%s: unexpected exception", fn);
+  }
+}
+
 void flash_attn_b200_set_path(int path) { g_path_request = path; }
 int flash_attn_b200_last_path(void) { return g_last_path; }
 int flash_attn_b200_last_launch_count(void) { return g_last_launches; }

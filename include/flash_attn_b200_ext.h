@@ -69,6 +69,23 @@ bool flash_attn_b200_varlen_bwd_shard(int batch_base, const void *dout, const vo
                                       int num_splits, fa_stream_t stream, uint64_t seed, uint64_t offset,
                                       const void *attn_mask, const int64_t *mask_dims);
 
+/* Dense backward for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference header.
+ * Same results as flash_attn_bwd (include/flash_attn.h) with num_splits = 0 and no attn_mask, but the two scratch
+ * tensors (softmax_d, dq_accum) are not arguments: they live in one static device array of
+ * FA_B200_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit.  The call performs no
+ * cudaMalloc / cudaFree / stream-ordered allocation.  Limit: 4 * batch * heads * seqlen_q_rounded *
+ * (1 + head_size_rounded) bytes (seqlen_q rounded up to 128, head_size to 32; e.g. B2 H8 S1024 D128 = 8.1 MiB)
+ * must not exceed FA_B200_STATIC_SCRATCH_BYTES, else the call returns false with a message and launches nothing.
+ * Every call on a device shares the array: what must start at zero is cleared by the call itself, and two calls
+ * that overlap on the GPU (different streams, or two host threads on one device) race on it -- serialise them. */
+#define FA_B200_STATIC_SCRATCH_BYTES (32u << 20)
+bool flash_attn_b200_bwd_static_scratch(const void *dout, const void *q, const void *k, const void *v,
+                                        const void *out, const void *softmax_lse, void *dq, void *dk, void *dv,
+                                        int batch_size, int seqlen_q, int seqlen_k, int num_heads, int num_heads_k,
+                                        int head_size, float p_dropout, float softmax_scale, bool is_causal,
+                                        bool is_bf16, fa_stream_t stream, uint64_t seed, uint64_t offset);
+
 /* Number of kernel launches the last successful call on this thread enqueued. */
 int flash_attn_b200_last_launch_count(void);
 
