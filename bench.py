@@ -302,7 +302,12 @@ def run_ours(args, rank, local_rank, world):
 
     sampler = ClockSampler(local_rank)
     sampler.start()
-    time.sleep(0.3)                   # let the fork finish before anything is timed
+    # nvidia-smi's start-up (driver attach, first query) stalls kernel launches for tens of ms: once it fell inside
+    # the 20 timed steps and cost them 70 ms (12.4 against 8.9 ms per step).  Wait for its first samples instead of
+    # a fixed 0.3 s, then warm up.
+    t_wait = time.time()
+    while len(sampler.samples) < 2 and time.time() - t_wait < 20.0:
+        time.sleep(0.05)
     for _ in range(max(args.warmup, 5)):
         w.step()
     lse = w.fwd(); fwd_path = api.last_path()

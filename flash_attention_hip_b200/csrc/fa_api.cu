@@ -70,11 +70,10 @@ bool fill_common(fa::Params &p, const char *fn, const Shape &s, float p_dropout,
   p.cu_q = varlen ? cu_q : nullptr;
   p.cu_k = varlen ? cu_k : nullptr;
   if (attn_mask) {
-    if (varlen) return fail("%s: attn_mask is not supported with packed (varlen) inputs", fn);
     if (!mask_dims) return fail("%s: attn_mask given but mask_dims is NULL", fn);
     if ((mask_dims[0] != 1 && mask_dims[0] != s.b) || (mask_dims[1] != 1 && mask_dims[1] != s.h) ||
         mask_dims[2] != s.sq || mask_dims[3] != s.sk)
-      return fail("%s: mask_dims must be {1|batch, 1|num_heads, seqlen_q, seqlen_k}", fn);
+      return fail("%s: mask_dims must be {1|batch, 1|num_heads, seqlen_q, seqlen_k} (packed inputs: the max_seqlen pair)", fn);
     p.mask = attn_mask;
     p.mask_b = mask_dims[0]; p.mask_h = mask_dims[1]; p.mask_sq = mask_dims[2]; p.mask_sk = mask_dims[3];
   }

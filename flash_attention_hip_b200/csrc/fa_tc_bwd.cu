@@ -75,8 +75,9 @@ struct BwdArgs {
   const float *lse, *softmax_d;
   const int32_t *cu_q, *cu_k;
   int b, sq, sk, sq_rounded, h, hk, nqt, batch_base;
-  const void *mask;      // additive bias [mask_b, mask_h, sq, sk] in the input dtype, or null (dense only)
-  int mask_b, mask_h;
+  const void *mask;      // additive bias [mask_b, mask_h, mask_sq, mask_sk] in the input dtype, or null; packed inputs:
+  int mask_b, mask_h;    // mask_sq / mask_sk = max_seqlen_q / max_seqlen_k, entry (row, col) counted from the sequence's start
+  int mask_sq, mask_sk;
   int *sem;              // deterministic dQ (num_splits == 1): one turn counter per (batch, head, query tile)
   int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
@@ -694,10 +695,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       uint16_t mbias[kMask ? 64 : 1];
       if constexpr (kMask) {
         const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
-            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * sq + q_base) * (size_t)sk + n_abs;
+            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * a.mask_sq + q_base) * (size_t)a.mask_sk + n_abs;
 #pragma unroll
         for (int c = 0; c < 64; ++c)
-          mbias[c] = (kv_valid && q_base + c < sq) ? __ldg(mp + (size_t)c * sk) : (uint16_t)0;
+          mbias[c] = (kv_valid && q_base + c < sq) ? __ldg(mp + (size_t)c * a.mask_sk) : (uint16_t)0;
       }
       ptx::mbar_wait(B.q_full + 8 * s, (g >> 1) & 1);    // LSE / D staged
       FA_TRACE_EV(trc, 11);
@@ -911,7 +912,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.batch_base = p.batch_base;
   a.d = p.d;
   a.nblk = (p.d + 31) / 32;
-  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
+  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h; a.mask_sq = (int)p.mask_sq; a.mask_sk = (int)p.mask_sk;
   a.scale = p.scale; a.scale_log2 = p.scale * kLog2e; a.rp_dropout = p.rp_dropout;
   a.keep_prob = kDropout ? 1.f - p.p_dropout : 1.f;
   a.drop_threshold = p.drop_threshold;
@@ -977,7 +978,7 @@ long long tc_bwd_scratch_floats(const Params &p) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 128 || p.d % 8) return false;   // d is padded to 64 or 128 by TMA zero fill
-  if (p.mask && (p.cu_q || p.deterministic)) return false;   // bias + ordered dQ: all-shapes kernels
+  if (p.mask && p.deterministic) return false;   // bias + ordered dQ: all-shapes kernels
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
   if (!p.dq_accum) return false;

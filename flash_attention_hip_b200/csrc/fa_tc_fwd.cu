@@ -154,8 +154,9 @@ struct TcFwdArgs {
   float *lse;
   const int32_t *cu_q, *cu_k;
   int b, sq, sk, h, hk, batch_base;
-  const void *mask;      // additive bias [mask_b, mask_h, sq, sk] in the input dtype, or null (dense only)
-  int mask_b, mask_h;
+  const void *mask;      // additive bias [mask_b, mask_h, mask_sq, mask_sk] in the input dtype, or null; packed inputs:
+  int mask_b, mask_h;    // mask_sq / mask_sk = max_seqlen_q / max_seqlen_k, entry (row, col) counted from the sequence's start
+  int mask_sq, mask_sk;
   int d;                 // real head_size (<= D, multiple of 8); columns [d, D) are TMA zero fill
   float scale_log2;      // softmax_scale * log2(e)
   float rp_dropout;
@@ -489,10 +490,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const uint16_t *mrow = nullptr;
     if (kMask && row < sq)
       mrow = static_cast<const uint16_t *>(a.mask) +
-             (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * sq + row) * (size_t)sk;
-    const bool mvec = (sk % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.mask) & 15) == 0);
+             (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * a.mask_sq + row) * (size_t)a.mask_sk;
+    const size_t msk = kMask ? (size_t)a.mask_sk : 0;         // row stride of the bias (== sk for dense inputs)
+    const bool mvec = (msk % 8 == 0) && ((reinterpret_cast<uintptr_t>(a.mask) & 15) == 0);
     const uint16_t *mbase = kMask ? static_cast<const uint16_t *>(a.mask) +
-        ((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * (size_t)sq * sk : nullptr;
+        ((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : head)) * (size_t)a.mask_sq * msk : nullptr;
     const int row_limit = row + shift;                // last visible key when causal
     const int tile_row0 = m0 + t * kTileM;
     uint32_t bh = 0;
@@ -533,14 +535,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if constexpr (kMaskStage) {
         mfast = mvec && (j * kTileN + kTileN <= sk);
         if (mfast) {
-          const uint16_t *mtile = mbase + (size_t)(tile_row0 + (warp & 3) * 32) * sk + j * kTileN;
+          const uint16_t *mtile = mbase + (size_t)(tile_row0 + (warp & 3) * 32) * msk + j * kTileN;
           const int rows_in = sq - (tile_row0 + (warp & 3) * 32);
           const uint32_t mstage = sbase + C::kSmemO + (uint32_t)(t * 4 + (warp & 3)) * 4096u;
           uint4 m0v[8];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const int r = (i % 8) * 4 + (lane >> 3);
-            const uint4 v = r < rows_in ? __ldg(reinterpret_cast<const uint4 *>(mtile + (size_t)r * sk + (i / 8) * 64 + (lane & 7) * 8))
+            const uint4 v = r < rows_in ? __ldg(reinterpret_cast<const uint4 *>(mtile + (size_t)r * msk + (i / 8) * 64 + (lane & 7) * 8))
                                         : make_uint4(0, 0, 0, 0);
             if (i < 8) m0v[i] = v; else mpre[i - 8] = v;
           }
@@ -869,7 +871,6 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 bool tc_fwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
   if (p.softmax_ret) return false;               // S_dmask output: all-shapes kernel
-  if (p.mask && p.cu_q) return false;
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;
@@ -912,7 +913,7 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.o_row = gqa_pack ? (long long)p.d : (long long)p.h * p.d;
   a.o_head = gqa_pack ? (long long)group * p.d : (long long)p.d;
   a.d = p.d;
-  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h;
+  a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h; a.mask_sq = (int)p.mask_sq; a.mask_sk = (int)p.mask_sk;
   a.scale_log2 = p.scale * kLog2e;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;

@@ -57,7 +57,9 @@ typedef struct CUstream_st *fa_stream_t;
  *   is_causal  bottom-right aligned: query i sees keys j <= i + seqlen_k - seqlen_q.
  *   attn_mask  optional additive bias in the input dtype with HOST dims
  *        mask_dims[4] = {b or 1, h or 1, seqlen_q, seqlen_k}; added to
- *        softmax_scale * q.k before the softmax. NULL = none.
+ *        softmax_scale * q.k before the softmax. NULL = none.  On the packed
+ *        entry points the bias is padded: {b or 1, h or 1, max_seqlen_q,
+ *        max_seqlen_k}, entry (row, col) counted from each sequence's first token.
  */
 bool flash_attn_fwd(const void * const q,
                     const void * const k,

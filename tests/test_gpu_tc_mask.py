@@ -100,3 +100,60 @@ def test_tc_mask_minus_inf_key_padding_d64_long(causal, sq, sk):
     gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
     assert gb["path"] == 2
     G.check_bwd(f"tc_mask/minus_inf_padding_d64_{'causal' if causal else 'full'}", pb, gb, rb, lp)
+
+
+# attn_mask on the PACKED entry points (reference flash_attn.h:65-66, :133-134).  Layout: the
+# bias is padded, [1|b, 1|h, max_seqlen_q, max_seqlen_k], entry (row, col) counted from each sequence's own start.
+PACKED = {
+    # name: (lens_q, lens_k, h, hk, d, kwargs, mask batch dim, mask head dim, -inf padding of the key tail)
+    "mix_d128_causal": ([300, 128, 517, 1], [300, 128, 517, 1], 4, 2, 128, dict(is_causal=True), 4, 1, False),
+    "cross_d64_bh": ([200, 77, 640], [328, 512, 130], 2, 2, 64, dict(), 3, 2, False),
+    "broadcast_b1h1_dropout": ([256, 384, 130], [256, 384, 130], 4, 4, 128, dict(p_dropout=0.15, seed=3, offset=8), 1, 1, False),
+    "key_padding_minus_inf_fp16": ([1024, 700, 256], [1024, 700, 256], 4, 1, 64, dict(is_bf16=False), 3, 1, True),
+    "many_items": ([520] * 40, [520] * 40, 8, 8, 64, dict(is_causal=True), 1, 8, False),
+}
+
+
+@pytest.mark.parametrize("name", list(PACKED))
+def test_tc_attn_mask_packed_fwd_bwd(name):
+    import gpu_util as G
+    lq, lk, h, hk, d, kw, mb, mh, pad = PACKED[name]
+    pb = cases.varlen(lq, lk, h, hk, d, **kw)
+    rng = np.random.default_rng(31)
+    m = rng.standard_normal((mb, mh, pb.seqlen_q, pb.seqlen_k), dtype=np.float32) * 2.0
+    if pad:                                      # the last third of every sequence's keys is invisible
+        for b in range(mb):
+            m[b, :, :, lk[b] - lk[b] // 3:] = -np.inf
+    pb.attn_mask = O.to_storage(m, pb.is_bf16)
+    q, k, v, dout = cases.make_inputs(pb, seed=17)
+    ref, lp_out = G.oracle_fwd(pb, q, k, v)
+    got = G.run_fwd(pb, q, k, v)
+    assert got["path"] == 2, "tcgen05 forward did not run"
+    G.check_fwd("tc_mask_packed/" + name, pb, got, ref, lp_out)
+    rb, lp = G.oracle_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
+    gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
+    assert gb["path"] == 2, "tcgen05 backward did not run"
+    G.check_bwd("tc_mask_packed/" + name, pb, gb, rb, lp)
+
+
+def test_packed_mask_equals_dense_mask_per_sequence():
+    """One packed call with a padded bias == one dense call per sequence with that sequence's corner of the bias."""
+    import torch
+    import gpu_util as G
+    from flash_attention_hip_b200 import api
+    lens = [384, 200, 129]
+    pb = cases.varlen(lens, lens, 4, 2, 128, is_causal=True)
+    rng = np.random.default_rng(8)
+    m = O.to_storage(rng.standard_normal((3, 4, 384, 384), dtype=np.float32), True)
+    pb.attn_mask = m
+    q, k, v, _ = cases.make_inputs(pb, seed=2, with_dout=False)
+    got = G.run_fwd(pb, q, k, v)
+    assert got["path"] == 2
+    packed_out = got["out"].reshape(-1, 4, 128)
+    for b, q0, sq, k0, sk in cases.seq_slices(pb):
+        one = cases.dense(1, sq, sk, 4, 2, 128, is_causal=True)
+        one.attn_mask = np.ascontiguousarray(m[b:b + 1, :, :sq, :sk])
+        g1 = G.run_fwd(one, q.reshape(-1, 4, 128)[q0:q0 + sq], k.reshape(-1, 2, 128)[k0:k0 + sk],
+                       v.reshape(-1, 2, 128)[k0:k0 + sk])
+        assert np.array_equal(g1["out"].reshape(sq, 4, 128), packed_out[q0:q0 + sq]), f"sequence {b}"
+        assert np.array_equal(g1["lse"][0], got["lse"][b, :, :sq])
