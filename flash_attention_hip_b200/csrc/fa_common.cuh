@@ -174,6 +174,7 @@ bool tc_fwd_supported(const Params &p);
 const char *launch_tc_fwd(const Params &p, cudaStream_t stream);
 bool tc_bwd_supported(const Params &p);
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream);
+const char *launch_tc_bwd_wide(const Params &p, cudaStream_t stream);   // head sizes 136..256 (fa_tc_bwd_wide.cu)
 
 // Ring context-parallel combine kernels (fa_cp.cu).
 const char *launch_cp_merge(void *o_acc, void *lse_acc, const void *o_blk, const void *lse_blk, int rows, int h,

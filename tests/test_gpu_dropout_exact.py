@@ -108,6 +108,10 @@ BWD_CASES = {
     "packed_d64_p25_sq_ne_sk": lambda s, o: cases.varlen([100, 300], [260, 128], 2, 2, 64, p_dropout=0.25, seed=s, offset=o,
                                                           batch_base=3),
     "many_items_d128_p10": lambda s, o: cases.dense(10, 512, 1024, 4, 4, 128, is_causal=True, p_dropout=0.1, seed=s, offset=o),
+    # head sizes above 128: fa_tc_bwd_wide.cu (two Philox calls per thread and step, one-word bit transposes)
+    "d256_p10_causal": lambda s, o: cases.dense(2, 384, 300, 2, 2, 256, is_causal=True, p_dropout=0.1, seed=s, offset=o),
+    "d192_p50_batch_base": lambda s, o: cases.dense(1, 257, 450, 2, 2, 192, p_dropout=0.5, seed=s, offset=o, batch_base=4),
+    "packed_d256_p25": lambda s, o: cases.varlen([200, 77, 300], [260, 77, 130], 2, 2, 256, p_dropout=0.25, seed=s, offset=o),
 }
 
 
@@ -152,7 +156,7 @@ def test_backward_transposed_mask_is_the_specification(name, si):
 
 
 @pytest.mark.parametrize("si", range(len(SEEDS)))
-@pytest.mark.parametrize("name", ["d128_p10", "d128_p50", "d64_p80", "packed_d128_p25"])
+@pytest.mark.parametrize("name", ["d128_p10", "d128_p50", "d64_p80", "packed_d128_p25", "d256_p25"])
 def test_backward_dp_mask_sign_probe(name, si):
     """The dP path of the backward applies the same keep bits with test + select.  With dP == 1 everywhere
     (V[:, 0] = 1, dO[:, 0] = 1) and K = identity block at key tile j:
@@ -163,6 +167,7 @@ def test_backward_dp_mask_sign_probe(name, si):
     pb = {"d128_p10": lambda: cases.dense(1, 300, 384, 2, 2, 128, p_dropout=0.1, seed=s, offset=o),
           "d128_p50": lambda: cases.dense(2, 257, 256, 2, 2, 128, p_dropout=0.5, seed=s, offset=o, batch_base=2),
           "d64_p80": lambda: cases.dense(1, 200, 320, 2, 2, 64, p_dropout=0.8, seed=s, offset=o),
+          "d256_p25": lambda: cases.dense(1, 200, 512, 2, 2, 256, p_dropout=0.25, seed=s, offset=o),
           "packed_d128_p25": lambda: cases.varlen([150, 260], [256, 384], 2, 2, 128, p_dropout=0.25, seed=s, offset=o)}[name]()
     d = pb.head_size
     rp = 1.0 / (1.0 - pb.p_dropout)

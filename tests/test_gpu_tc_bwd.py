@@ -40,6 +40,23 @@ CASES = {
     "many_items_b10h8s1024d64": lambda: cases.dense(10, 1024, 1024, 8, 8, 64, is_causal=True, p_dropout=0.1, seed=3),
     "many_items_gqa_s1152d128": lambda: cases.dense(6, 1152, 1152, 16, 4, 128, is_causal=True, p_dropout=0.2, seed=8, offset=5),
     "many_items_ragged_full": lambda: cases.dense(40, 200, 333, 4, 4, 128),
+    # head sizes 136..256: fa_tc_bwd_wide.cu (items = key tile x half of the head dimension, 64-query steps)
+    "d256_s128": lambda: cases.dense(1, 128, 128, 2, 2, 256),
+    "d256_s64_one_step": lambda: cases.dense(1, 64, 128, 1, 1, 256),
+    "d256_causal": lambda: cases.dense(2, 384, 384, 2, 2, 256, is_causal=True),
+    "d256_ragged_gqa": lambda: cases.dense(1, 300, 450, 4, 2, 256),
+    "d256_causal_gqa_drop": lambda: cases.dense(2, 200, 200, 4, 2, 256, is_causal=True, p_dropout=0.1, seed=8, offset=3),
+    "d192_dropout": lambda: cases.dense(1, 257, 257, 2, 2, 192, is_causal=True, p_dropout=0.1, seed=3, offset=9),
+    "d192_ragged": lambda: cases.dense(1, 130, 333, 2, 2, 192),
+    "d160_fp16": lambda: cases.dense(1, 200, 333, 2, 1, 160, is_bf16=False),
+    "d160_sq_gt_sk_causal_fp16": lambda: cases.dense(1, 300, 150, 2, 1, 160, is_causal=True, is_bf16=False),
+    "d136_sq_gt_sk_causal": lambda: cases.dense(1, 450, 300, 2, 2, 136, is_causal=True),
+    "d224_tiny_5x700": lambda: cases.dense(1, 5, 700, 2, 1, 224, is_causal=True),
+    "d256_packed": lambda: cases.varlen([200, 77, 300], [200, 77, 300], 4, 2, 256, is_causal=True),
+    "d200_packed_sq_ne_sk": lambda: cases.varlen([100, 300], [260, 128], 2, 2, 200),
+    "d136_packed": lambda: cases.varlen([100, 1, 77], [130, 64, 77], 2, 2, 136, is_causal=True),
+    "d256_many_items": lambda: cases.dense(6, 640, 640, 8, 4, 256, is_causal=True, p_dropout=0.2, seed=8, offset=5),
+    "d192_many_items_packed": lambda: cases.varlen([520] * 24, [520] * 24, 4, 4, 192),
 }
 
 
