@@ -440,6 +440,11 @@ def run_ours(args, rank, local_rank, world):
             ring_c5 = _ring_c5(torch, dist, api, rank, world, dev)
         except Exception as exc:  # noqa: BLE001 -- reported in the line, never hides the headline
             ring_c5 = {"error": repr(exc)}
+        try:
+            from flash_attention_hip_b200 import ring as _ring
+            _ring.close_comms()
+        except Exception:  # noqa: BLE001
+            pass
 
     if rank != 0:
         if world > 1:

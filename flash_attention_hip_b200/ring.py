@@ -16,6 +16,13 @@ three dense calls (c = chunk length, src = owner of the visiting K/V):
 Non-causal attention takes any contiguous sharding and calls q x kv non-causally every step.
 
 Dropout is not offered here (its stream is indexed by local coordinates); p_dropout must be 0.
+
+Two engines run this schedule.  On CUDA tensors (the product): the library's own C entry points
+`flash_attn_b200_ring_fwd` / `flash_attn_b200_ring_bwd` (csrc/fa_ring.cu: ncclSend / ncclRecv on a communication
+stream one step ahead of the kernels, event-chained; one merge kernel at the end of the forward) -- this module
+then only bootstraps the communicator (`RingComm`) and owns the workspace.  With an explicit `ops` engine (the
+CPU tests pass an oracle-backed one under gloo): the Python loop below over `torch.distributed` P2P, which is the
+same schedule step for step.
 """
 from __future__ import annotations
 
@@ -24,7 +31,110 @@ from typing import List, Optional
 import torch
 import torch.distributed as dist
 
+import ctypes
+
 from .shard import CudaOps
+
+ENGINE = "C entry points flash_attn_b200_ring_fwd / _bwd (csrc/fa_ring.cu) over ncclSend / ncclRecv"
+
+
+class RingComm:
+    """The library's ring communicator for one process group: NCCL unique id from rank 0, handed round with
+    torch.distributed (any backend), then `flash_attn_b200_ring_comm_create` on every rank (its device current)."""
+
+    def __init__(self, group=None):
+        from . import api
+        self.api, self.lib = api, api.lib()
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        L = self.lib
+        vp, i, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+        L.flash_attn_b200_ring_unique_id.argtypes = [vp]; L.flash_attn_b200_ring_unique_id.restype = ctypes.c_bool
+        L.flash_attn_b200_ring_comm_create.argtypes = [vp, i, i, ctypes.POINTER(vp)]
+        L.flash_attn_b200_ring_comm_create.restype = ctypes.c_bool
+        L.flash_attn_b200_ring_comm_destroy.argtypes = [vp]; L.flash_attn_b200_ring_comm_destroy.restype = None
+        for name in ("fwd", "bwd"):
+            f = getattr(L, f"flash_attn_b200_ring_{name}_workspace_bytes")
+            f.argtypes = [i] * 6; f.restype = sz
+        L.flash_attn_b200_ring_fwd.argtypes = [vp] * 7 + [sz] + [i] * 5 + [ctypes.c_float, ctypes.c_bool, ctypes.c_bool, vp]
+        L.flash_attn_b200_ring_fwd.restype = ctypes.c_bool
+        L.flash_attn_b200_ring_bwd.argtypes = [vp] * 11 + [sz] + [i] * 5 + [ctypes.c_float, ctypes.c_bool, ctypes.c_bool, vp]
+        L.flash_attn_b200_ring_bwd.restype = ctypes.c_bool
+        ident = [None]
+        if self.world > 1:
+            if self.rank == 0:
+                buf = ctypes.create_string_buffer(128)
+                if not L.flash_attn_b200_ring_unique_id(buf):
+                    raise api.FlashAttnError(api.last_error())
+                ident = [buf.raw]
+            src = dist.get_global_rank(group, 0) if group is not None else 0
+            dist.broadcast_object_list(ident, src=src, group=group)
+        self.handle = vp()
+        if not L.flash_attn_b200_ring_comm_create(ident[0], self.world, self.rank, ctypes.byref(self.handle)):
+            raise api.FlashAttnError(api.last_error())
+        self._ws = {}
+
+    def workspace(self, kind, b, s, h, hk, d, device):
+        n = getattr(self.lib, f"flash_attn_b200_ring_{kind}_workspace_bytes")(self.world, b, s, h, hk, d)
+        ws = self._ws.get(kind)
+        if ws is None or ws.numel() < n or ws.device != device:
+            ws = self._ws[kind] = torch.empty(max(n, 256), dtype=torch.uint8, device=device)
+        return ws
+
+    def close(self):
+        if self.handle:
+            self.lib.flash_attn_b200_ring_comm_destroy(self.handle)
+            self.handle = None
+
+
+_COMMS = {}
+
+
+def _comm_for(group) -> RingComm:
+    key = id(group) if group is not None else None
+    if key not in _COMMS:
+        _COMMS[key] = RingComm(group)
+    return _COMMS[key]
+
+
+def close_comms() -> None:
+    """Destroys the cached communicators (call before destroy_process_group)."""
+    for c in _COMMS.values():
+        c.close()
+    _COMMS.clear()
+
+
+def _c_fwd(q, k, v, causal, scale, group):
+    c = _comm_for(group)
+    b, s, h, d = q.shape
+    hk = k.shape[2]
+    assert q.is_contiguous() and k.is_contiguous() and v.is_contiguous()
+    out = torch.empty_like(q)
+    lse = torch.empty((b, h, s), dtype=torch.float32, device=q.device)
+    ws = c.workspace("fwd", b, s, h, hk, d, q.device)
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    ok = c.lib.flash_attn_b200_ring_fwd(c.handle, P(q), P(k), P(v), P(out), P(lse), P(ws), ws.numel(), b, s, h, hk, d,
+                                        scale, causal, q.dtype == torch.bfloat16,
+                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if not ok:
+        raise c.api.FlashAttnError("flash_attn_b200_ring_fwd failed: " + c.api.last_error())
+    return out, lse
+
+
+def _c_bwd(dout, q, k, v, out, lse, causal, scale, group):
+    c = _comm_for(group)
+    b, s, h, d = q.shape
+    hk = k.shape[2]
+    for t in (dout, q, k, v, out, lse):
+        assert t.is_contiguous()
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    ws = c.workspace("bwd", b, s, h, hk, d, q.device)
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    ok = c.lib.flash_attn_b200_ring_bwd(c.handle, P(dout), P(q), P(k), P(v), P(out), P(lse), P(dq), P(dk), P(dv), P(ws),
+                                        ws.numel(), b, s, h, hk, d, scale, causal, q.dtype == torch.bfloat16,
+                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if not ok:
+        raise c.api.FlashAttnError("flash_attn_b200_ring_bwd failed: " + c.api.last_error())
+    return dq, dk, dv
 
 
 # ---- zig-zag layout helpers (used by callers, the bench and the tests) -------------------------
@@ -80,12 +190,14 @@ def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: 
     """Forward over the ring.  q [b, s_local, h, d], k/v [b, s_local, hk, d]: this rank's shard
     (zig-zag when causal).  Returns (out [b, s_local, h, d], lse fp32 [b, h, s_local]) equal to the
     rank's rows of full-sequence attention."""
-    ops = ops if ops is not None else CudaOps()
-    world, rank = dist.get_world_size(group), dist.get_rank(group)
     b, s, h, d = q.shape
     if causal and s % 2:
         raise ValueError("causal ring attention needs an even local length (zig-zag chunks)")
     scale = float(d) ** -0.5 if scale is None else scale
+    if ops is None and q.is_cuda:
+        return _c_fwd(q, k, v, causal, scale, group)
+    ops = ops if ops is not None else CudaOps()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
     o_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
     lse_acc = torch.full((b, h, s), float("inf"), dtype=torch.float32, device=q.device)
     kv_cur = torch.stack([k, v]).contiguous()
@@ -109,10 +221,12 @@ def ring_attn_bwd(dout: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch
                   lse: torch.Tensor, *, causal: bool, scale: Optional[float] = None, group=None, ops=None):
     """Backward over the ring from the forward's (out, lse).  The dK/dV partial sums travel with
     their K/V chunk (fp32) and arrive home after the last hop.  Returns (dq, dk, dv)."""
-    ops = ops if ops is not None else CudaOps()
-    world, rank = dist.get_world_size(group), dist.get_rank(group)
     b, s, h, d = q.shape
     scale = float(d) ** -0.5 if scale is None else scale
+    if ops is None and q.is_cuda:
+        return _c_bwd(dout, q, k, v, out, lse, causal, scale, group)
+    ops = ops if ops is not None else CudaOps()
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
     dq_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
     kv_cur = torch.stack([k, v]).contiguous()
     kv_nxt = torch.empty_like(kv_cur)

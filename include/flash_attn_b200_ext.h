@@ -9,6 +9,7 @@
 #define FLASH_ATTN_B200_EXT_H_
 
 #include <stdbool.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "flash_attn.h"
@@ -104,6 +105,37 @@ bool flash_attn_b200_cp_merge(void *o_acc, void *lse_acc, const void *o_blk, con
 bool flash_attn_b200_cp_accumulate(void *acc_f32, const void *blk, int64_t n, bool is_bf16, fa_stream_t stream);
 /* dst[i] (16-bit) = src_f32[i], i < n. */
 bool flash_attn_b200_cp_store(void *dst, const void *src_f32, int64_t n, bool is_bf16, fa_stream_t stream);
+
+/* ---- ring context parallel as a library call ------------------------------------------------------
+ * No counterpart in the reference header.  One process (or host thread) per GPU; the N ranks of one NVLink box each
+ * hold a shard of the sequence: q [b, s_local, h, d], k / v [b, s_local, hk, d] (causal: the ZIG-ZAG shard -- chunks
+ * r and 2N-1-r of the 2N equal chunks of the full sequence, s_local even; non-causal: any contiguous split).
+ * ring_fwd returns this rank's rows of full-sequence attention: out [b, s_local, h, d], lse fp32 [b, h, s_local].
+ * ring_bwd takes the forward's (out, lse) and returns dq, dk, dv of the shard.  K/V chunks (and, in the backward,
+ * the fp32 dK/dV partial sums) travel round the ring with ncclSend / ncclRecv on a communication stream owned by the
+ * comm object, one step ahead of the kernels that consume them; everything else is enqueued on `stream`.  Every
+ * rank must make the same call.  No dropout, no attn_mask in this mode.  NCCL is bound at run time (dlopen of
+ * libnccl.so.2): nothing else in this library needs it.
+ *
+ * Bootstrap like NCCL's own: one rank calls ring_unique_id, hands the FA_B200_RING_ID_BYTES to the others by any
+ * means, every rank (its device current) calls ring_comm_create.  ring_comm_from_nccl borrows a communicator the
+ * caller already has (not destroyed by ring_comm_destroy).
+ * `workspace`: device memory of at least ring_*_workspace_bytes(...), 256-byte aligned, owned by the caller. */
+#define FA_B200_RING_ID_BYTES 128
+typedef struct fa_ring_comm fa_ring_comm_t;
+bool flash_attn_b200_ring_unique_id(void *id128);
+bool flash_attn_b200_ring_comm_create(const void *id128, int nranks, int rank, fa_ring_comm_t **comm);
+bool flash_attn_b200_ring_comm_from_nccl(void *nccl_comm, int nranks, int rank, fa_ring_comm_t **comm);
+void flash_attn_b200_ring_comm_destroy(fa_ring_comm_t *comm);
+size_t flash_attn_b200_ring_fwd_workspace_bytes(int nranks, int b, int s_local, int h, int hk, int d);
+size_t flash_attn_b200_ring_bwd_workspace_bytes(int nranks, int b, int s_local, int h, int hk, int d);
+bool flash_attn_b200_ring_fwd(fa_ring_comm_t *comm, const void *q, const void *k, const void *v, void *out, void *lse,
+                              void *workspace, size_t workspace_bytes, int b, int s_local, int h, int hk, int d,
+                              float softmax_scale, bool is_causal, bool is_bf16, fa_stream_t stream);
+bool flash_attn_b200_ring_bwd(fa_ring_comm_t *comm, const void *dout, const void *q, const void *k, const void *v,
+                              const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
+                              size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
+                              bool is_causal, bool is_bf16, fa_stream_t stream);
 
 /* Developer builds only (-DFA_TRACE): copies the in-kernel event timeline of warp role `role`
  * of the forward (kernel 0) or backward (kernel 1) tcgen05 kernel's traced CTA into dst as

@@ -108,3 +108,21 @@ def test_ring_world1_equals_plain_calls():
                 assert float((got.float() - ref.float()).abs().max() / ref.float().abs().max()) < 2e-3
     finally:
         dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_ring_c_entry_points_multi_gpu(world):
+    """flash_attn_b200_ring_fwd / _bwd (csrc/fa_ring.cu) over `world` GPUs of this box against a single-GPU
+    full-sequence run (tests/cuda/ring_check.py: 2e-2 relative on out / dq / dk / dv, 1e-3 on LSE, every rank).
+    Skipped where fewer GPUs are visible; bench.py's `ring_c5` key repeats the check inside the scaling run."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29540 + world), os.path.join(root, "tests", "cuda", "ring_check.py"), "8192", "1", "notime"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("parity OK") == world, r.stdout[-3000:]
