@@ -162,6 +162,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   // Query tile of inner iteration `it`.  Ordered (deterministic) dQ walks the tiles from the last one
   // down: every key-tile CTA of a causal problem then starts on the same query tile and the turns
   // form a pipeline, instead of CTA j first waiting for the diagonal tile of all its predecessors.
+  // (Round 2 measured the alternative -- every item walks upwards from its diagonal tile, turn order = key tiles
+  // descending, which is also the order they naturally arrive in, persistent queue -- at 305 / 513 TFLOP/s causal /
+  // full against 423 / 565 for this one: what bounds the ordered mode is not the order but the link between two
+  // consecutive adders of a tile -- bulk reduce-adds performed, fence, release, acquire poll: ~7 us -- which sits
+  // on every step of every item's walk whichever way the walks are laid out.  profiles/r02c_ordered_dq.log)
   constexpr bool descending = kOrdered;
 #define FA_ITEM_LOCALS(I)                                                                                      \
   const int j = (I).j, hk = (I).hk, bidx = (I).bidx, sq = (I).sq, sk = (I).sk, qrow0 = (I).qrow0,              \

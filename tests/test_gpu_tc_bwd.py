@@ -40,6 +40,10 @@ CASES = {
     "many_items_b10h8s1024d64": lambda: cases.dense(10, 1024, 1024, 8, 8, 64, is_causal=True, p_dropout=0.1, seed=3),
     "many_items_gqa_s1152d128": lambda: cases.dense(6, 1152, 1152, 16, 4, 128, is_causal=True, p_dropout=0.2, seed=8, offset=5),
     "many_items_ragged_full": lambda: cases.dense(40, 200, 333, 4, 4, 128),
+    # non-causal shapes for the ordered-dQ walk (cyclic start tile): more key tiles than query tiles and the reverse
+    "det_full_s1024_gqa": lambda: cases.dense(3, 1024, 1024, 8, 2, 128, p_dropout=0.1, seed=4, offset=2),
+    "det_full_sq_lt_sk": lambda: cases.dense(2, 300, 1100, 4, 4, 64),
+    "det_full_sq_gt_sk": lambda: cases.dense(2, 1100, 300, 4, 2, 128),
     # head sizes 136..256: fa_tc_bwd_wide.cu (items = key tile x half of the head dimension, 64-query steps)
     "d256_s128": lambda: cases.dense(1, 128, 128, 2, 2, 256),
     "d256_s64_one_step": lambda: cases.dense(1, 64, 128, 1, 1, 256),
@@ -84,8 +88,11 @@ def test_tc_fwd_bwd_chain():
     G.check_bwd("tc_fwd_bwd_chain", pb, gb, rb, None)
 
 
-@pytest.mark.parametrize("name", ["d128_s384_causal", "gqa_8to2", "ragged_300x450", "dropout_d128", "d96_causal_gqa",
-                                  "c2_small_b2h4s2048d128"])
+@pytest.mark.parametrize("name", ["d128_s384_causal", "gqa_8to2", "ragged_300x450", "ragged_300x450_causal", "dropout_d128",
+                                  "d96_causal_gqa", "c2_small_b2h4s2048d128", "sq_gt_sk_causal_empty_rows",
+                                  "tiny_5x700_causal", "fp16_d64", "many_items_b10h8s1024d64",
+                                  "many_items_gqa_s1152d128", "many_items_ragged_full", "det_full_s1024_gqa",
+                                  "det_full_sq_lt_sk", "det_full_sq_gt_sk"])
 def test_tc_bwd_deterministic_is_bit_reproducible_and_correct(name):
     """num_splits == 1 (reference flash_attn.h:94): key tiles add into dQ in a fixed order, so two runs
     agree bit for bit; the result stays within the parity tolerance."""

@@ -89,3 +89,21 @@ def test_varlen_neighbour_poison():
     v2[100:] = O.to_storage(np.full(v2[100:].shape, np.inf, np.float32), True)
     b = G.run_fwd(pb, q, k, v2)
     assert np.array_equal(a["out"][:100], b["out"][:100])
+
+
+@pytest.mark.parametrize("name", ["ragged_d128_causal_gqa", "sq_ne_sk", "sq_ne_sk_causal", "dropout_causal", "empty_seq_inside",
+                                  "c4_mix_d128_causal_h8"])
+def test_tc_varlen_bwd_deterministic(name):
+    """num_splits == 1 on packed inputs: bit-reproducible and within the parity tolerance (the ordered-dQ turn
+    ranks are computed from each sequence's own lengths)."""
+    import gpu_util as G
+    pb = CASES[name]()
+    q, k, v, dout = cases.make_inputs(pb, seed=11)
+    ref = O.forward(pb, q, k, v)
+    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    a = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"], deterministic=True)
+    b = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"], deterministic=True)
+    assert a["path"] == 2 and b["path"] == 2
+    for t in ("dq", "dk", "dv"):
+        assert np.array_equal(a[t], b[t]), t
+    G.check_bwd("tc_varlen_deterministic/" + name, pb, a, rb, None)
