@@ -51,7 +51,7 @@ def load_peaks():
     return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
-BWD_LAUNCHES = ("bwd_preprocess_kernel", "dq_accum_memset", "tc_bwd_kernel", "dq_convert_kernel")
+BWD_LAUNCHES = ("bwd_preprocess_kernel", "tc_bwd_kernel", "dq_convert_kernel")   # (the preprocess kernel also zeroes dq_accum)
 
 
 def load_traffic():
