@@ -152,7 +152,9 @@ bool bwd_impl(const char *fn, const void *dout, const void *q, const void *k, co
     return fail("%s: tcgen05 path requested but this problem is outside it", fn);
   const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
   // softmax_d; the tcgen05 backward's dq_accum is zeroed by the same kernel
-  const char *err = fa::launch_bwd_preprocess(p, st, use_tc ? p.dq_accum : nullptr, use_tc ? fa::tc_bwd_scratch_floats(p) : 0);
+  // (num_splits == 1 on the tcgen05 path writes dq without the scratch: nothing to zero)
+  const bool zero_acc = use_tc && !p.deterministic;
+  const char *err = fa::launch_bwd_preprocess(p, st, zero_acc ? p.dq_accum : nullptr, zero_acc ? fa::tc_bwd_scratch_floats(p) : 0);
   if (!err) err = use_tc ? fa::launch_tc_bwd(p, st) : fa::launch_generic_bwd(p, st);
   if (err) return fail("%s: %s", fn, err);
   g_last_path = use_tc ? FA_B200_PATH_TCGEN05 : FA_B200_PATH_GENERIC;
@@ -402,7 +404,7 @@ bool flash_attn_b200_bwd_static_scratch(const void *dout, const void *q, const v
     if (const char *e = static_scratch_base(&base)) return fail("%s: %s", fn, e);
     const Shape s{batch_size, seqlen_q, seqlen_k, static_cast<int>(sq_r), (seqlen_k + 127) / 128 * 128,
                   num_heads, num_heads_k, head_size, static_cast<int>(d_r)};
-    // num_splits = 0: the ordered-dQ mode keeps its turn counters in a stream-ordered temporary (an allocation)
+    // num_splits = 0: dQ by reduce-adds in arrival order, the header's default
     return bwd_impl(fn, dout, q, k, v, out, base, softmax_lse, nullptr, nullptr, false, dq, dk, dv,
                     base + d_floats, s, p_dropout, softmax_scale, is_causal, is_bf16, /*num_splits=*/0, stream,
                     seed, offset, nullptr, nullptr);

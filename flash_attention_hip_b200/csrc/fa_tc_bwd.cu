@@ -79,13 +79,13 @@ struct BwdArgs {
   const void *mask;      // additive bias [mask_b, mask_h, mask_sq, mask_sk] in the input dtype, or null; packed inputs:
   int mask_b, mask_h;    // mask_sq / mask_sk = max_seqlen_q / max_seqlen_k, entry (row, col) counted from the sequence's start
   int mask_sq, mask_sk;
-  int *sem;              // deterministic dQ (num_splits == 1): one turn counter per (batch, head, query tile)
   int d, nblk;           // real head_size (<= D, multiple of 8; the rest is TMA zero fill); 32-column blocks of dq_accum   // sq/sk/nqt: dense values or packed maxima
   float scale, scale_log2, rp_dropout;
   float keep_prob;       // 1 - p_dropout.  dS is computed as P o (keep o dP - D (1 - p)) = (1 - p) dS; the factor 1 / (1 - p)
                          // rides on the final scales of dQ and dK (one multiply per output element, not per score)
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
+  int hk_kv;             // K/V heads (mode 2 overwrites hk with the query head count: its items are per query head)
   int nkt, n_items;      // key tiles per sequence (dense: of sk; packed: of the longest); items = nkt * hk * b
   int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
   SchedSlot *sched;      // global item counter of this launch (self-resetting pool slot, fa_common.cuh)
@@ -102,13 +102,27 @@ struct BwdBars {
       dq_full, dq_drained, acc_done, epi_tmem_free, epi_smem_free, sched_full /*[2]*/, sched_empty /*[2]*/;
 };
 
-template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
+// kMode: 0 = the fused kernel described at the top (dQ by reduce-adds in arrival order).
+// Deterministic dQ (num_splits == 1, reference flash_attn.h:94) runs as TWO launches of this kernel without any atomic:
+//   1 = dK / dV only: the fused kernel minus GEMM (5) and the dQ drain;
+//   2 = dQ only, MIRRORED: one item = one 128-QUERY tile of one (batch, query head), resident operands Q and dO
+//       (in the K and V slots), streamed operands K and V (in the Q and dO slots): the same GEMMs then give
+//       (1) S = Q K^T, (2) dP = dO V^T with TMEM lane = QUERY row, and (4) accumulates dQ = dS K in the dK columns.
+//       LSE / D are per LANE (two scalars per item instead of staged vectors), the causal mask and the dropout draw
+//       are the row-wise ones of the forward (no bit transposes), nothing leaves through dq_accum.
+// 7 GEMM units per tile pair instead of 5 and twice the exponentials, but no serialised turns: round 1's ordered
+// reduce-adds (a turn counter per query tile) ran at 423 / 565 TFLOP/s causal / full because the link between two
+// consecutive adders of a tile (adds performed, fence, release, acquire poll: ~7 us) sat on every step; an upward
+// walk with turn order = arrival order was measured too: 305 / 513 (profiles/r02c_ordered_dq.log).
+template <int D, bool kBF16, bool kDropout, bool kMask, int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
               const __grid_constant__ CUtensorMap tmap_dk, const __grid_constant__ CUtensorMap tmap_dv,
               const BwdArgs a) {
   using C = Cfg<D>;
+  constexpr bool kMirror = kMode == 2;
+  static_assert(kMode == 0 || !kMask, "attn_mask rides the fused kernel only");
   // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
   // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
   constexpr bool kEarlyDrain = true;
@@ -135,10 +149,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     size_t qtok0, ktok0;
     bool valid;
   };
-  const int group = a.h / a.hk;
+  const int group_real = a.h / a.hk_kv;
+  const int group = kMirror ? 1 : group_real;          // mirrored: `hk` below IS the query head, no loop over a group
   auto decode = [&](int L) {
     Item I;
     I.j = L % a.nkt; I.hk = (L / a.nkt) % a.hk; I.bidx = L / (a.nkt * a.hk);
+    if constexpr (kMirror) {                           // a.nkt / a.hk hold the query tile and query head counts
+      I.j = a.causal ? a.nkt - 1 - I.j : I.j;          // causal: the last query tile sees the most keys: heaviest first
+    }
     I.sq = a.sq; I.sk = a.sk; I.qrow0 = 0; I.krow0 = 0; I.bcoord = I.bidx;   // TMA row origin / batch coordinate
     I.qtok0 = (size_t)I.bidx * a.sq; I.ktok0 = (size_t)I.bidx * a.sk;        // first token of this sequence
     if (a.cu_q) {
@@ -146,8 +164,19 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       I.sq = a.cu_q[I.bidx + 1] - I.qrow0; I.sk = a.cu_k[I.bidx + 1] - I.krow0;
       I.qtok0 = (size_t)I.qrow0; I.ktok0 = (size_t)I.krow0; I.bcoord = 0;
     }
-    I.valid = I.j * kT < I.sk;                   // packed: this sequence may have no such key tile
     I.shift = I.sk - I.sq;                       // causal: key n visible to row r iff n <= r + shift
+    if constexpr (kMirror) {
+      // `j` = my QUERY tile, the loop walks the key tiles 0 .. n_it - 1 that its rows see
+      I.valid = I.j * kT < I.sq;
+      int nk = (I.sk + kT - 1) / kT;
+      if (a.causal) {
+        const int last_key = I.j * kT + kT - 1 + I.shift;      // last key the tile's last row sees
+        nk = last_key < 0 ? 0 : min(nk, last_key / kT + 1);
+      }
+      I.i_min = 0; I.n_i = nk; I.n_it = nk;
+      return I;
+    }
+    I.valid = I.j * kT < I.sk;                   // packed: this sequence may have no such key tile
     const int nqt = (I.sq + kT - 1) / kT;        // query tiles of this sequence
     I.i_min = 0;
     if (a.causal) {
@@ -159,15 +188,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     return I;
   };
   if (!a.persistent && !decode((int)blockIdx.x).valid) return;
-  // Query tile of inner iteration `it`.  Ordered (deterministic) dQ walks the tiles from the last one
-  // down: every key-tile CTA of a causal problem then starts on the same query tile and the turns
-  // form a pipeline, instead of CTA j first waiting for the diagonal tile of all its predecessors.
-  // (Round 2 measured the alternative -- every item walks upwards from its diagonal tile, turn order = key tiles
-  // descending, which is also the order they naturally arrive in, persistent queue -- at 305 / 513 TFLOP/s causal /
-  // full against 423 / 565 for this one: what bounds the ordered mode is not the order but the link between two
-  // consecutive adders of a tile -- bulk reduce-adds performed, fence, release, acquire poll: ~7 us -- which sits
-  // on every step of every item's walk whichever way the walks are laid out.  profiles/r02c_ordered_dq.log)
-  constexpr bool descending = kOrdered;
+  // Query tile of inner iteration `it` (mirrored: key tile).
+  constexpr bool descending = false;
 #define FA_ITEM_LOCALS(I)                                                                                      \
   const int j = (I).j, hk = (I).hk, bidx = (I).bidx, sq = (I).sq, sk = (I).sk, qrow0 = (I).qrow0,              \
             krow0 = (I).krow0, bcoord = (I).bcoord, shift = (I).shift, i_min = (I).i_min, n_i = (I).n_i,      \
@@ -267,24 +289,31 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         mapped_b = bidx;
         set ^= 1;
       }
+      // resident pair (K and V slots) and streamed pair (Q and dO slots): K, V | Q, dO -- mirrored: Q, dO | K, V
+      const CUtensorMap *res_a = kMirror ? mq : mk, *res_b = kMirror ? mdo : mv;
+      const CUtensorMap *str_a = kMirror ? mk : mq, *str_b = kMirror ? mv : mdo;
+      const int res_row0 = kMirror ? qrow0 : krow0, str_row0 = kMirror ? krow0 : qrow0;
       if (lane == 0) {
         ptx::mbar_arrive_expect_tx(B.kv_full, 2 * C::kTile);
         for (int c = 0; c < D / 64; ++c) {
-          ptx::tma_load_4d(sbase + C::kK + c * C::kSub, mk, B.kv_full, c * 64, hk, krow0 + j * kT, bcoord);
-          ptx::tma_load_4d(sbase + C::kV + c * C::kSub, mv, B.kv_full, c * 64, hk, krow0 + j * kT, bcoord);
+          ptx::tma_load_4d(sbase + C::kK + c * C::kSub, res_a, B.kv_full, c * 64, hk, res_row0 + j * kT, bcoord);
+          ptx::tma_load_4d(sbase + C::kV + c * C::kSub, res_b, B.kv_full, c * 64, hk, res_row0 + j * kT, bcoord);
         }
       }
       for (int it = 0; it < n_it; ++it) {
         const int hq = hk * group + it / n_i, i = q_tile_of(it);
+        const int str_head = kMirror ? hk / group_real : hq;
         const int g = g0 + it, s = g & 1;
         if (g >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((g >> 1) - 1) & 1);
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.q_full + 8 * s, C::kTile);
           for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kQ + s * C::kTile + c * C::kSub, mq, B.q_full + 8 * s,
-                             c * 64, hq, qrow0 + i * kT, bcoord);
+            ptx::tma_load_4d(sbase + C::kQ + s * C::kTile + c * C::kSub, str_a, B.q_full + 8 * s,
+                             c * 64, str_head, str_row0 + i * kT, bcoord);
         }
-        {
+        if constexpr (kMirror) {
+          if (lane == 0) ptx::mbar_arrive(B.q_full + 8 * s);     // (LSE / D are per lane here: nothing to stage)
+        } else {
           // staged NEGATED: -LSE * log2(e) (-inf past the sequence end => P = 0 there), -D = -rowsum(dO o O)
           const float *lse = a.lse + ((size_t)bidx * a.h + hq) * a.sq;
           const float *dd = a.softmax_d + ((size_t)bidx * a.h + hq) * a.sq_rounded;
@@ -304,7 +333,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.do_full, C::kTile);
           for (int c = 0; c < D / 64; ++c)
-            ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, mdo, B.do_full, c * 64, hq, qrow0 + i * kT, bcoord);
+            ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, str_b, B.do_full, c * 64, str_head, str_row0 + i * kT, bcoord);
         }
       }
       g0 += n_it;
@@ -351,21 +380,24 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         FA_TRACE_EV(tr, 1);
         ptx::mbar_wait(B.do_full, g & 1);
         FA_TRACE_EV(tr, 2);
-        if (g > 0) ptx::mbar_wait(B.dq_drained, (g - 1) & 1);             // dP^T shares TMEM with dQ
+        if (kMode == 0 && g > 0) ptx::mbar_wait(B.dq_drained, (g - 1) & 1);   // dP^T shares TMEM with dQ
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 3);
         gemm_kk(tDP, b16, C::kV, b16, C::kDO);                               // (2) dP^T(it)
         ptx::mma_commit(B.dp_full);
-        ptx::mbar_wait(B.p_ready, g & 1);
+        if constexpr (kMirror) ptx::mma_commit(B.do_empty);                  // no (3) here: the dO slot is free after (2)
+        ptx::mbar_wait(B.p_ready, g & 1);                                    // (mirrored: S has been read, nothing written)
         // the first dV / dK MMAs of an item overwrite the accumulators: the previous item's epilogue must have read them
         if (it == 0 && nv >= 1) ptx::mbar_wait(B.epi_tmem_free, (nv - 1) & 1);
         ptx::tc_fence_after();
         FA_TRACE_EV(tr, 4);
+        if constexpr (!kMirror) {
 #pragma unroll
-        for (int ks = 0; ks < kT / 16; ++ks)                               // (3) dV += P^T dO
-          ptx::mma_ts(tDV, tS + (ks / 4) * 64 + (ks % 4) * 8,
-                      ptx::smem_desc_at(hi_mn, b16, C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
-        ptx::mma_commit(B.do_empty);
+          for (int ks = 0; ks < kT / 16; ++ks)                             // (3) dV += P^T dO
+            ptx::mma_ts(tDV, tS + (ks / 4) * 64 + (ks % 4) * 8,
+                        ptx::smem_desc_at(hi_mn, b16, C::kDO + ks * 2048), id_k_mn, it > 0 || ks > 0);
+          ptx::mma_commit(B.do_empty);
+        }
         if (it + 1 < n_it) {
           ptx::mbar_wait(B.q_full + 8 * (s ^ 1), ((g + 1) >> 1) & 1);
           ptx::tc_fence_after();
@@ -378,11 +410,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         FA_TRACE_EV(tr, 6);
         // dQ first: it heads the longest dependency chain of the loop (dQ -> drain -> dP^T(it+1) -> dS
         // -> dQ(it+1), through the shared tensor-memory columns); dK only feeds its own accumulator
+        if constexpr (kMode == 0) {
 #pragma unroll
-        for (int ks = 0; ks < kT / 16; ++ks)                               // (5) dQ = dS K
-          ptx::mma_ss(tDP, ptx::smem_desc_at(hi_mn, b16, C::kDS + ks * 2048),
-                      ptx::smem_desc_at(hi_mn, b16, C::kK + ks * 2048), id_mn_mn, ks > 0);
-        ptx::mma_commit(B.dq_full);
+          for (int ks = 0; ks < kT / 16; ++ks)                             // (5) dQ = dS K
+            ptx::mma_ss(tDP, ptx::smem_desc_at(hi_mn, b16, C::kDS + ks * 2048),
+                        ptx::smem_desc_at(hi_mn, b16, C::kK + ks * 2048), id_mn_mn, ks > 0);
+          ptx::mma_commit(B.dq_full);
+        }
 #pragma unroll
         for (int ks = 0; ks < kT / 16; ++ks) {                             // (4) dK += dS^T Q
           const uint32_t aoff = (ks / 4) * C::kSub + (ks % 4) * 32;
@@ -425,12 +459,13 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if (sm >= (uint32_t)ptx::kMaxSm) __trap();
       const uint32_t d0 = sbase + C::kDesc;
       uint8_t *gen0 = smem_raw + C::kDesc;
-      mdk = ptx::patch_rows(tmap_dk, &g_bwd_slots[sm][set][4], d0 + 512, gen0 + 512, (uint32_t)(krow0 + sk), lane);
-      mdv = ptx::patch_rows(tmap_dv, &g_bwd_slots[sm][set][5], d0 + 640, gen0 + 640, (uint32_t)(krow0 + sk), lane);
+      const uint32_t out_rows = kMirror ? (uint32_t)(qrow0 + sq) : (uint32_t)(krow0 + sk);   // mirrored: the map is dq's
+      mdk = ptx::patch_rows(tmap_dk, &g_bwd_slots[sm][set][4], d0 + 512, gen0 + 512, out_rows, lane);
+      mdv = ptx::patch_rows(tmap_dv, &g_bwd_slots[sm][set][5], d0 + 640, gen0 + 640, out_rows, lane);
       mapped_b = bidx;
       set ^= 1;
     }
-    for (int it = 0; it < n_it; ++it) {
+    for (int it = 0; kMode == 0 && it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
       float *gdst = a.dq_accum + ((((size_t)bidx * a.h + hq) * a.nqt + i) * a.nblk) * 4096;
@@ -448,21 +483,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::mbar_arrive(B.dq_drained);
       }
       FA_TRACE_EV(trd, 22);
-      // Deterministic dQ: the key tiles add into a query tile in ascending order.  CTA j takes its
-      // turn when the counter reads j (CTAs 0..j-1 of this (batch, kv head) were dispatched before
-      // it, so the wait cannot deadlock) and passes it on once its reduce-adds have completed.
-      int *turn = nullptr;
-      if constexpr (kOrdered) {
-        turn = a.sem + ((size_t)bidx * a.h + hq) * a.nqt + i;
-        if (leader) {
-          const long long t0 = clock64();
-          int seen;
-          do {
-            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(turn) : "memory");
-            if (clock64() - t0 > (1ll << 32)) __trap();
-          } while (seen != j);
-        }
-      }
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
         if (c >= a.nblk) break;                        // head_size < D: the last blocks are all zero
@@ -489,11 +509,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         ++cc;
       }
-      if (kOrdered && leader) {
-        ptx::tma_store_wait<0>();                      // my adds for this tile have been performed
-        __threadfence();
-        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(turn), "r"(j + 1) : "memory");
-      }
     }
     // ---- epilogue: dK_j, dV_j -> global ----------------------------------------------------
     // A drain thread owns one ROW of dK / dV (TMEM lane = key row).  The tiles leave like the dQ blocks do:
@@ -506,7 +521,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::tc_fence_after();
     FA_TRACE_EV(trd, 23);
 #pragma unroll
-    for (int which = 0; which < 2; ++which) {
+    for (int which = kMirror ? 1 : 0; which < 2; ++which) {        // mirrored: only the dK columns are used (they hold dQ)
       const float mul = which ? a.scale * a.rp_dropout : a.rp_dropout;
 #pragma unroll
       for (int c = 0; c < D / 64; ++c) {
@@ -538,7 +553,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::fence_proxy_async_smem();
         ptx::named_bar_sync(1, 128);
         if (leader) {
-          if (c * 64 < a.d) ptx::tma_store_4d(which ? mdk : mdv, buf, c * 64, hk, krow0 + j * kT, bcoord);
+          if (c * 64 < a.d) ptx::tma_store_4d(which ? mdk : mdv, buf, c * 64, hk, (kMirror ? qrow0 : krow0) + j * kT, bcoord);
           ptx::tma_store_commit();
         }
         ++cc;
@@ -575,17 +590,31 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     const Item I = decode(L);
     if (!I.valid) continue;
     FA_ITEM_LOCALS(I);
-    const int n_abs = j * kT + n;
-    const bool kv_valid = n_abs < sk;
+    const int n_abs = j * kT + n;                      // my key -- mirrored: my QUERY row
+    const bool kv_valid = n_abs < (kMirror ? sq : sk);
     const bool ragged_k = j * kT + kT > sk;            // this item's key tile runs past the sequence end
+    // mirrored: LSE / D of my own row, negated and scaled like the staged vectors of the other modes
+    float nl_mine = -INFINITY, nd_mine = 0.f;
+    if constexpr (kMirror) {
+      if (kv_valid) {
+        nl_mine = -a.lse[((size_t)bidx * a.h + hk) * a.sq + n_abs] * kLog2e;
+        nd_mine = -a.softmax_d[((size_t)bidx * a.h + hk) * a.sq_rounded + n_abs] * a.keep_prob;
+      }
+    }
     uint32_t pc[4][4];
     auto ctr_init = [&](int it_) {
       const int hq_ = hk * group + it_ / n_i, i_ = q_tile_of(it_);
       const uint32_t bh_ = (uint32_t)((a.batch_base + bidx) * a.h + hq_);
 #pragma unroll
       for (int blk = 0; blk < 4; ++blk) {
-        pc[blk][0] = (uint32_t)(i_ * kT + w * 64 + blk * 16 + (lane & 15));
-        pc[blk][1] = (uint32_t)(n_abs >> 4); pc[blk][2] = bh_; pc[blk][3] = a.ctr3;
+        if constexpr (kMirror) {       // my row, the four 16-key blocks of my 64 columns: the forward's own mapping
+          pc[blk][0] = (uint32_t)n_abs;
+          pc[blk][1] = (uint32_t)((i_ * kT + w * 64 + blk * 16) >> 4);
+        } else {
+          pc[blk][0] = (uint32_t)(i_ * kT + w * 64 + blk * 16 + (lane & 15));
+          pc[blk][1] = (uint32_t)(n_abs >> 4);
+        }
+        pc[blk][2] = bh_; pc[blk][3] = a.ctr3;
       }
     };
     if constexpr (kDropout) {
@@ -623,10 +652,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         // 16x16 bit transposes inside each half-warp (four at once, two per word): butterfly over
         // lane bits 8, 4, 2, 1 -- 8 shuffles instead of the 64 a gather per (query, key) pair costs
-        bit_transpose_stage<8>(w01, w23, lane);
-        bit_transpose_stage<4>(w01, w23, lane);
-        bit_transpose_stage<2>(w01, w23, lane);
-        bit_transpose_stage<1>(w01, w23, lane);
+        if constexpr (!kMirror) {           // (mirrored: the words already are my row's keep bits, column by column)
+          bit_transpose_stage<8>(w01, w23, lane);
+          bit_transpose_stage<4>(w01, w23, lane);
+          bit_transpose_stage<2>(w01, w23, lane);
+          bit_transpose_stage<1>(w01, w23, lane);
+        }
         keep_lo = w01;                    // bit t: keep(query q_base + t, my key)
         keep_hi = w23;
       }
@@ -656,8 +687,14 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_wait_ld();
       }
       FA_TRACE_EV(trc, 30);
-      const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
-      const int lim = n_abs - shift;                     // causal: visible iff q >= lim
+      if constexpr (kMirror) {              // S is in registers and nothing is written back: S(it + 1) may overwrite it
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(B.p_ready);
+      }
+      // causal, fused / dK-dV: my key n_abs is visible to query q iff q >= lim; mirrored: my row sees key k iff k <= -lim
+      const bool diag = a.causal && (kMirror ? (q_base + 63 > j * kT + shift) : (j * kT + kT - 1 > q_base + shift));   // warp-uniform
+      const int lim = kMirror ? -(n_abs + shift) : n_abs - shift;
+      const bool ragged = kMirror ? (i * kT + kT > sk) : ragged_k;
       float cs = c2;
       if constexpr (kMask) {                                      // s <- s * scale_log2 + bias * log2 e
 #pragma unroll
@@ -672,7 +709,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if constexpr (kDropout) ctr_init(it + 1);           // (one wasted draw after the last iteration)
 #pragma unroll
       for (int c = 0; c < 64; c += 4) {
-        const float4 nl = ld_shared_f32x4(stat + 4 * c);                  // -lse2 of 4 query columns
+        const float4 nl = kMirror ? make_float4(nl_mine, nl_mine, nl_mine, nl_mine)
+                                  : ld_shared_f32x4(stat + 4 * c);        // -lse2 of 4 query columns
         float2 x = __ffma2_rn(make_float2(p[c], p[c + 1]), c2v, make_float2(nl.x, nl.y));
         float2 y = __ffma2_rn(make_float2(p[c + 2], p[c + 3]), c2v, make_float2(nl.z, nl.w));
         p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
@@ -700,12 +738,17 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
       FA_TRACE_EV(trc, 31);
-      if (diag || ragged_k) {                            // CTA/warp-uniform: only diagonal and last key tiles
+      if (diag || ragged) {                              // CTA/warp-uniform: only diagonal and last key tiles
 #pragma unroll
-        for (int c = 0; c < 64; ++c)
-          if (!kv_valid || (diag && q_base + c < lim)) p[c] = 0.f;
+        for (int c = 0; c < 64; ++c) {
+          if constexpr (kMirror) {                       // column = key q_base + c
+            if (q_base + c >= sk || (diag && q_base + c > -lim)) p[c] = 0.f;
+          } else {
+            if (!kv_valid || (diag && q_base + c < lim)) p[c] = 0.f;
+          }
+        }
       }
-      {
+      if constexpr (!kMirror) {
         uint32_t pk[32];
 #pragma unroll
         for (int c = 0; c < 32; ++c) pk[c] = pack2(p[2 * c], p[2 * c + 1], kBF16);
@@ -724,8 +767,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_wait_st();
         FA_TRACE_EV(trc, 33);
       }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(B.p_ready);
+      if constexpr (!kMirror) {
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(B.p_ready);
+      }
       FA_TRACE_EV(trc, 13);
 
       ptx::mbar_wait(B.dp_full, g & 1);
@@ -758,7 +803,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               g23.x = (kb & 4u) ? g23.x : 0.f;
               g23.y = (kb & 8u) ? g23.y : 0.f;
             }
-            const float4 nd = ld_shared_f32x4(stat + 512 + 4 * cq);        // -D of 4 query columns
+            const float4 nd = kMirror ? make_float4(nd_mine, nd_mine, nd_mine, nd_mine)
+                                      : ld_shared_f32x4(stat + 512 + 4 * cq);   // -D of 4 query columns
             const float2 e01 = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(g01, make_float2(nd.x, nd.y)));
             const float2 e23 = __fmul2_rn(make_float2(p[cq + 2], p[cq + 3]), __fadd2_rn(g23, make_float2(nd.z, nd.w)));
             ds[c / 2] = pack2(e01.x, e01.y, kBF16);
@@ -831,7 +877,7 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
 std::atomic<SchedSlot *> g_bwd_sched_addr[kMaxCachedDevices];   // device address of g_bwd_sched, per device
 std::atomic<unsigned> g_bwd_ticket{0};
 
-template <int D, bool kBF16, bool kDropout, bool kMask, bool kOrdered>
+template <int D, bool kBF16, bool kDropout, bool kMask, int kMode>
 const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
   CUtensorMap tq, tk, tv, tdo;
@@ -842,9 +888,14 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   if ((e = make_tmap_rows(&tdo, p.dout, kBF16, p.d, p.h, p.sq, nb, kT))) return e;
   if ((e = make_tmap_rows(&tk, p.k, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
   if ((e = make_tmap_rows(&tv, p.v, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
-  CUtensorMap tdk, tdv;      // the dK / dV tiles leave through bulk tensor stores
-  if ((e = make_tmap_rows(&tdk, p.dk, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
-  if ((e = make_tmap_rows(&tdv, p.dv, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+  CUtensorMap tdk, tdv;      // the dK / dV tiles leave through bulk tensor stores (mode 2: dQ, through the dK map)
+  if (kMode == 2) {
+    if ((e = make_tmap_rows(&tdk, p.dq, kBF16, p.d, p.h, p.sq, nb, kT))) return e;
+    tdv = tdk;
+  } else {
+    if ((e = make_tmap_rows(&tdk, p.dk, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+    if ((e = make_tmap_rows(&tdv, p.dv, kBF16, p.d, p.hk, p.sk, nb, kT))) return e;
+  }
 
   BwdArgs a;
   a.dk = p.dk; a.dv = p.dv; a.dq_accum = p.dq_accum; a.lse = p.lse; a.softmax_d = p.softmax_d;
@@ -862,16 +913,21 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.key1 = (uint32_t)(p.seed >> 32);
   a.ctr3 = (uint32_t)p.offset;
   a.causal = p.causal ? 1 : 0;
+  a.hk_kv = p.hk;
 
-  auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask, kOrdered>;
+  auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask, kMode>;
   int dev = 0, sm_count = 0;
   if ((e = current_device(&dev, &sm_count))) return e;
   static std::atomic<uint64_t> smem_opt_in{0};   // per instantiation, one bit per device
   if ((e = ensure_dynamic_smem(kern, (int)C::kBytes, dev, smem_opt_in))) return e;
   a.nkt = (p.sk + kT - 1) / kT;
   a.n_items = a.nkt * p.hk * p.b;
-  // ordered dQ: its turns assume CTA j starts after CTAs 0..j-1; no more items than SMs: no counter needed
-  a.persistent = (!kOrdered && a.n_items > sm_count) ? 1 : 0;
+  if (kMode == 2) {          // mirrored: items are (query tile, QUERY head, batch); the kernel reads them from nkt / hk
+    a.nkt = a.nqt;
+    a.hk = p.h;
+    a.n_items = a.nqt * p.h * p.b;
+  }
+  a.persistent = a.n_items > sm_count ? 1 : 0;   // no more items than SMs: no counter needed
   a.sched = nullptr;
   int grid = a.n_items;
   if (a.persistent) {
@@ -879,23 +935,11 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
     if ((e = take_sched_slot(g_bwd_sched, dev, g_bwd_sched_addr, g_bwd_ticket, &a.sched))) return e;
   }
 
-  // (dq_accum was zeroed by the preprocess kernel: tc_bwd_scratch_floats)
-  // num_splits == 1: turn counters for the ordered dQ accumulation, a stream-ordered temporary (the
-  // ABI has no argument for them; freed on the same stream right after the kernel, on every exit)
-  a.sem = nullptr;
-  if (kOrdered) {
-    const size_t sem_bytes = (size_t)p.b * p.h * a.nqt * sizeof(int);
-    if (cudaMallocAsync(reinterpret_cast<void **>(&a.sem), sem_bytes, stream) != cudaSuccess)
-      return "cudaMallocAsync(dq turn counters) failed";
-    if (cudaMemsetAsync(a.sem, 0, sem_bytes, stream) != cudaSuccess) {
-      cudaFreeAsync(a.sem, stream);
-      return "cudaMemsetAsync(dq turn counters) failed";
-    }
-  }
+  // (mode 0: dq_accum was zeroed by the preprocess kernel: tc_bwd_scratch_floats)
   kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, tdk, tdv, a);
   cudaError_t err = cudaGetLastError();
-  if (a.sem) cudaFreeAsync(a.sem, stream);
   if (err != cudaSuccess) return cudaGetErrorString(err);
+  if (kMode != 0) return nullptr;          // the two-launch deterministic backward never touches dq_accum
   dim3 cgrid(a.nqt, p.h, p.b);
   dq_convert_kernel<D, kBF16><<<cgrid, 256, 0, stream>>>(p.dq_accum, p.dq, p.cu_q, p.sq, p.h, a.nqt, p.scale * p.rp_dropout, a.d,
                                                          a.nblk);
@@ -930,13 +974,22 @@ bool tc_bwd_supported(const Params &p) {
   return true;
 }
 
+namespace {
+// num_splits == 1: dK / dV, then dQ, no atomics anywhere (see kMode at the kernel)
+template <int D, bool kBF16, bool kDropout>
+const char *launch_det(const Params &p, cudaStream_t stream) {
+  const char *e = launch_tc_bwd_t<D, kBF16, kDropout, false, 1>(p, stream);
+  return e ? e : launch_tc_bwd_t<D, kBF16, kDropout, false, 2>(p, stream);
+}
+}  // namespace
+
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   if (p.d > 128) return launch_tc_bwd_wide(p, stream);
   const bool drop = p.p_dropout > 0.f;
 #define FA_MASKED(DD, BF, DR)                                                              \
-  (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, false>(p, stream)                            \
-          : p.deterministic ? launch_tc_bwd_t<DD, BF, DR, false, true>(p, stream)          \
-                            : launch_tc_bwd_t<DD, BF, DR, false, false>(p, stream))
+  (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, 0>(p, stream)                                \
+          : p.deterministic ? launch_det<DD, BF, DR>(p, stream)                            \
+                            : launch_tc_bwd_t<DD, BF, DR, false, 0>(p, stream))
 #define FA_DISPATCH(DD)                                                                          \
   if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                          \
                              : FA_MASKED(DD, true, false);                        \

@@ -1,5 +1,5 @@
-"""The entry points inside a CUDA graph: INTEGRATION.md says the two internal temporaries (item counter,
-turn counters) are stream-ordered allocations and therefore capturable.  Capture forward + backward once,
+"""The entry points inside a CUDA graph: INTEGRATION.md says no entry point allocates (the item counters of the
+persistent kernels are a self-resetting pool in the library's own device memory).  Capture forward + backward once,
 replay, and compare with the eager result bit for bit (same seed/offset, non-deterministic dQ order aside)."""
 import pytest
 
