@@ -122,7 +122,6 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               const BwdArgs a) {
   using C = Cfg<D>;
   constexpr bool kMirror = kMode == 2;
-  static_assert(kMode == 0 || !kMask, "attn_mask rides the fused kernel only");
   // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
   // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
   constexpr bool kEarlyDrain = true;
@@ -666,7 +665,24 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // depend on S^T either -- fetched before the wait for it, so the loads' latency is spent waiting anyway
       // (lanes hold consecutive keys: each load instruction reads 64 contiguous bytes of one mask row)
       uint16_t mbias[kMask ? 64 : 1];
-      if constexpr (kMask) {
+      if constexpr (kMask && kMirror) {
+        // mirrored: my row's 64 bias values are 128 contiguous bytes (columns = keys q_base .. q_base + 63)
+        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
+            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * a.mask_sq + n_abs) * (size_t)a.mask_sk + q_base;
+        const bool fast = kv_valid && q_base + 64 <= sk && a.mask_sk % 8 == 0 && (reinterpret_cast<uintptr_t>(a.mask) & 15) == 0;
+        if (fast) {
+#pragma unroll
+          for (int v8 = 0; v8 < 8; ++v8) {
+            const uint4 x = __ldg(reinterpret_cast<const uint4 *>(mp) + v8);
+            const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mbias[8 * v8 + e] = (uint16_t)(w4[e / 2] >> (16 * (e & 1)));
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 64; ++c) mbias[c] = (kv_valid && q_base + c < sk) ? __ldg(mp + c) : (uint16_t)0;
+        }
+      } else if constexpr (kMask) {
         const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
             (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * a.mask_sq + q_base) * (size_t)a.mask_sk + n_abs;
 #pragma unroll
@@ -964,7 +980,6 @@ long long tc_bwd_scratch_floats(const Params &p) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
-  if (p.mask && p.deterministic) return false;   // bias + ordered dQ: all-shapes kernels
   if (p.d > 128 && (p.mask || p.deterministic)) return false;   // fa_tc_bwd_wide.cu offers neither
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
@@ -976,10 +991,10 @@ bool tc_bwd_supported(const Params &p) {
 
 namespace {
 // num_splits == 1: dK / dV, then dQ, no atomics anywhere (see kMode at the kernel)
-template <int D, bool kBF16, bool kDropout>
+template <int D, bool kBF16, bool kDropout, bool kMask>
 const char *launch_det(const Params &p, cudaStream_t stream) {
-  const char *e = launch_tc_bwd_t<D, kBF16, kDropout, false, 1>(p, stream);
-  return e ? e : launch_tc_bwd_t<D, kBF16, kDropout, false, 2>(p, stream);
+  const char *e = launch_tc_bwd_t<D, kBF16, kDropout, kMask, 1>(p, stream);
+  return e ? e : launch_tc_bwd_t<D, kBF16, kDropout, kMask, 2>(p, stream);
 }
 }  // namespace
 
@@ -987,9 +1002,9 @@ const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   if (p.d > 128) return launch_tc_bwd_wide(p, stream);
   const bool drop = p.p_dropout > 0.f;
 #define FA_MASKED(DD, BF, DR)                                                              \
-  (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, 0>(p, stream)                                \
-          : p.deterministic ? launch_det<DD, BF, DR>(p, stream)                            \
-                            : launch_tc_bwd_t<DD, BF, DR, false, 0>(p, stream))
+  (p.deterministic ? (p.mask ? launch_det<DD, BF, DR, true>(p, stream) : launch_det<DD, BF, DR, false>(p, stream)) \
+                   : (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, 0>(p, stream)             \
+                             : launch_tc_bwd_t<DD, BF, DR, false, 0>(p, stream)))
 #define FA_DISPATCH(DD)                                                                          \
   if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                          \
                              : FA_MASKED(DD, true, false);                        \

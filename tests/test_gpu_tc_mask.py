@@ -157,3 +157,29 @@ def test_packed_mask_equals_dense_mask_per_sequence():
                        v.reshape(-1, 2, 128)[k0:k0 + sk])
         assert np.array_equal(g1["out"].reshape(sq, 4, 128), packed_out[q0:q0 + sq]), f"sequence {b}"
         assert np.array_equal(g1["lse"][0], got["lse"][b, :, :sq])
+
+
+@pytest.mark.parametrize("name", ["bh_d128", "b1_h1_broadcast_causal", "b_h1_d64_ragged", "padding_minus_inf", "sk_not_multiple_of_8",
+                                  "dropout_and_mask", "many_tiles_bh", "packed:mix_d128_causal", "packed:cross_d64_bh"])
+def test_tc_attn_mask_deterministic_bwd(name):
+    """attn_mask together with num_splits == 1: the two-launch deterministic backward (dK/dV, then the mirrored dQ pass,
+    which reads the bias row-wise) on the tcgen05 kernels: bit-reproducible and within the parity tolerance."""
+    import gpu_util as G
+    if name.startswith("packed:"):
+        lq, lk, h, hk, d, kw, mb, mh, pad = PACKED[name[7:]]
+        pb = cases.varlen(lq, lk, h, hk, d, **kw)
+        rng = np.random.default_rng(31)
+        pb.attn_mask = O.to_storage(rng.standard_normal((mb, mh, pb.seqlen_q, pb.seqlen_k), dtype=np.float32) * 2.0, pb.is_bf16)
+    else:
+        mk, mb, mh, pad, neg = CASES[name]
+        pb = mk()
+        pb.attn_mask = _mask(pb, mb, mh, seed=21, pad_from=pad, neg=neg)
+    q, k, v, dout = cases.make_inputs(pb, seed=13)
+    ref = O.forward(pb, q, k, v)
+    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    a = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"], deterministic=True)
+    b = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"], deterministic=True)
+    assert a["path"] == 2 and b["path"] == 2, "tcgen05 backward did not run"
+    for t in ("dq", "dk", "dv"):
+        assert np.array_equal(a[t], b[t]), t
+    G.check_bwd("tc_mask_deterministic/" + name, pb, a, rb, None)
