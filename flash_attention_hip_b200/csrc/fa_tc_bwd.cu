@@ -60,7 +60,7 @@ struct Cfg {
   static constexpr uint32_t kDQ = kDS + 2 * kSub;     // 2 x 16 KB fp32 staging blocks
   static constexpr uint32_t kStat = kDQ + 2 * 16384;  // 2 stages x {lse2[128], D[128]} fp32
   static constexpr uint32_t kBar = kStat + 2 * 1024;
-  static constexpr uint32_t kNumBars = 20;
+  static constexpr uint32_t kNumBars = 22;
   static constexpr uint32_t kDesc = kBar + 256;        // 6 x 128 B tensor-map staging (packed inputs)
   static constexpr uint32_t kBytes = kDesc + 6 * 128;
   static_assert(kBytes <= 232448, "over the 227 KB a CTA may ask for");
@@ -85,6 +85,7 @@ struct BwdArgs {
                          // rides on the final scales of dQ and dK (one multiply per output element, not per score)
   uint32_t drop_threshold, key0, key1, ctr3;
   int causal;
+  int mask_tma;          // kMode 1 with attn_mask: bias tiles arrive by TMA (tmap_bias)
   int hk_kv;             // K/V heads (mode 2 overwrites hk with the query head count: its items are per query head)
   int nkt, n_items;      // key tiles per sequence (dense: of sk; packed: of the longest); items = nkt * hk * b
   int persistent;        // 1: CTAs pull items from *sched until none are left; 0: item = blockIdx.x
@@ -99,7 +100,8 @@ namespace {
 
 struct BwdBars {
   uint32_t kv_full, q_full /*[2]*/, q_empty /*[2]*/, do_full, do_empty, s_full, dp_full, p_ready, ds_ready,
-      dq_full, dq_drained, acc_done, epi_tmem_free, epi_smem_free, sched_full /*[2]*/, sched_empty /*[2]*/;
+      dq_full, dq_drained, acc_done, epi_tmem_free, epi_smem_free, sched_full /*[2]*/, sched_empty /*[2]*/,
+      bias_full, bias_empty;
 };
 
 // kMode: 0 = the fused kernel described at the top (dQ by reduce-adds in arrival order).
@@ -119,8 +121,12 @@ __global__ void __launch_bounds__(kThreads, 1)
 tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
               const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
               const __grid_constant__ CUtensorMap tmap_dk, const __grid_constant__ CUtensorMap tmap_dv,
-              const BwdArgs a) {
+              const __grid_constant__ CUtensorMap tmap_bias, const BwdArgs a) {
   using C = Cfg<D>;
+  // attn_mask in the dK / dV pass (kMode 1): the pass has no dQ to drain, so the 32 KB of dQ staging are free during
+  // an item's loop and hold the step's [128 query x 128 key] bias tile, brought by TMA one step ahead (a lane owns a
+  // key COLUMN of the bias here: read from global memory that is 64 two-byte loads per lane and step, latency exposed)
+  constexpr bool kBiasTma = kMask && kMode == 1;
   constexpr bool kMirror = kMode == 2;
   // register split of the 16 warps (2048 per lane in total): without dropout the drain warps
   // hold a whole dQ tile; with dropout the compute warps need the room for the keep-bit exchange
@@ -205,7 +211,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   B.do_empty = bar0 + 48;    B.s_full = bar0 + 56;     B.dp_full = bar0 + 64;   B.p_ready = bar0 + 72;
   B.ds_ready = bar0 + 80;    B.dq_full = bar0 + 88;    B.dq_drained = bar0 + 96; B.acc_done = bar0 + 104;
   B.epi_tmem_free = bar0 + 112; B.epi_smem_free = bar0 + 120; B.sched_full = bar0 + 128; B.sched_empty = bar0 + 144;
-  static_assert(C::kNumBars >= 20, "barrier block too small");
+  B.bias_full = bar0 + 160;  B.bias_empty = bar0 + 168;
+  static_assert(C::kNumBars >= 22 && C::kNumBars * 8 + 32 <= 256, "barrier block too small");
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem_raw + C::kBar + C::kNumBars * 8);
   volatile int *sched_item = reinterpret_cast<volatile int *>(tmem_slot + 2);   // [2]
 
@@ -218,7 +225,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::mbar_init(B.p_ready, 256);   ptx::mbar_init(B.ds_ready, 256);
     ptx::mbar_init(B.dq_full, 1);     ptx::mbar_init(B.dq_drained, 128);
     ptx::mbar_init(B.acc_done, 1);
-    ptx::mbar_init(B.epi_tmem_free, 128);  ptx::mbar_init(B.epi_smem_free, 1);   // (epi_smem_free: unused)
+    ptx::mbar_init(B.epi_tmem_free, 128);  ptx::mbar_init(B.epi_smem_free, 1);   // (epi_smem_free: bias tiles only)
+    ptx::mbar_init(B.bias_full, 1);        ptx::mbar_init(B.bias_empty, 256);
     for (int t = 0; t < 2; ++t) {
       ptx::mbar_init(B.sched_full + 8 * t, 1);
       ptx::mbar_init(B.sched_empty + 8 * t, 1 + 128 + 256);    // MMA lane, drain warps, compute warps
@@ -303,6 +311,17 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         const int hq = hk * group + it / n_i, i = q_tile_of(it);
         const int str_head = kMirror ? hk / group_real : hq;
         const int g = g0 + it, s = g & 1;
+        if constexpr (kBiasTma) {
+          if (a.mask_tma) {
+            if (g >= 1) ptx::mbar_wait(B.bias_empty, (g - 1) & 1);                  // the compute warps have read tile g - 1
+            if (it == 0 && nv >= 1) ptx::mbar_wait(B.epi_smem_free, (nv - 1) & 1);  // the last item's dK / dV have left the staging
+            if (lane == 0) {
+              ptx::mbar_arrive_expect_tx(B.bias_full, kT * kT * 2);
+              ptx::tma_load_4d(sbase + C::kDQ, &tmap_bias, B.bias_full, j * kT, i * kT, a.mask_h == 1 ? 0 : hq,
+                               a.mask_b == 1 ? 0 : bidx);
+            }
+          }
+        }
         if (g >= 2) ptx::mbar_wait(B.q_empty + 8 * s, ((g >> 1) - 1) & 1);
         if (lane == 0) {
           ptx::mbar_arrive_expect_tx(B.q_full + 8 * s, C::kTile);
@@ -559,6 +578,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       }
     }
     FA_TRACE_EV(trd, 24);
+    if constexpr (kBiasTma) {
+      if (a.mask_tma && leader) {          // the staging blocks have been read by the stores: the next item's bias tile may land
+        ptx::tma_store_wait_read<0>();
+        ptx::mbar_arrive(B.epi_smem_free);
+      }
+    }
     g0 += n_it;
     ++nv;
     }   // items
@@ -682,6 +707,16 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
 #pragma unroll
           for (int c = 0; c < 64; ++c) mbias[c] = (kv_valid && q_base + c < sk) ? __ldg(mp + c) : (uint16_t)0;
         }
+      } else if (kBiasTma && a.mask_tma) {
+        ptx::mbar_wait(B.bias_full, g & 1);
+        const uint16_t *bt = reinterpret_cast<const uint16_t *>(smem_raw + C::kDQ) + (size_t)(w * 64) * kT + n;   // [query][key]
+        const bool rows_ragged = q_base + 64 > sq;         // warp-uniform
+#pragma unroll
+        for (int c = 0; c < 64; ++c) {
+          const uint16_t vb = bt[c * kT];
+          mbias[c] = (kv_valid && (!rows_ragged || q_base + c < sq)) ? vb : (uint16_t)0;   // (padding may hold anything)
+        }
+        ptx::mbar_arrive(B.bias_empty);
       } else if constexpr (kMask) {
         const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
             (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * a.mask_sq + q_base) * (size_t)a.mask_sk + n_abs;
@@ -893,6 +928,11 @@ dq_convert_kernel(const float *__restrict__ acc, void *__restrict__ dq, const in
 std::atomic<SchedSlot *> g_bwd_sched_addr[kMaxCachedDevices];   // device address of g_bwd_sched, per device
 std::atomic<unsigned> g_bwd_ticket{0};
 
+// bias rows of whole 16-byte units from a 16-byte aligned base: what a TMA tensor map needs
+bool mask_tma_ok(const Params &p) {
+  return p.mask && p.mask_sk % 8 == 0 && (reinterpret_cast<uintptr_t>(p.mask) & 15) == 0;
+}
+
 template <int D, bool kBF16, bool kDropout, bool kMask, int kMode>
 const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   using C = Cfg<D>;
@@ -931,6 +971,13 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   a.causal = p.causal ? 1 : 0;
   a.hk_kv = p.hk;
 
+  CUtensorMap tbias = tq;    // (a valid map either way; only read when mask_tma is set)
+  a.mask_tma = 0;
+  if (kMask && kMode == 1 && mask_tma_ok(p)) {
+    if ((e = make_tmap_bias(&tbias, p.mask, kBF16, (uint64_t)p.mask_sk, (uint64_t)p.mask_sq, (uint64_t)p.mask_h, (uint64_t)p.mask_b, kT)))
+      return e;
+    a.mask_tma = 1;
+  }
   auto kern = tc_bwd_kernel<D, kBF16, kDropout, kMask, kMode>;
   int dev = 0, sm_count = 0;
   if ((e = current_device(&dev, &sm_count))) return e;
@@ -952,7 +999,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   }
 
   // (mode 0: dq_accum was zeroed by the preprocess kernel: tc_bwd_scratch_floats)
-  kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, tdk, tdv, a);
+  kern<<<grid, kThreads, C::kBytes, stream>>>(tq, tk, tv, tdo, tdk, tdv, tbias, a);
   cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return cudaGetErrorString(err);
   if (kMode != 0) return nullptr;          // the two-launch deterministic backward never touches dq_accum
@@ -1002,9 +1049,10 @@ const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
   if (p.d > 128) return launch_tc_bwd_wide(p, stream);
   const bool drop = p.p_dropout > 0.f;
 #define FA_MASKED(DD, BF, DR)                                                              \
-  (p.deterministic ? (p.mask ? launch_det<DD, BF, DR, true>(p, stream) : launch_det<DD, BF, DR, false>(p, stream)) \
-                   : (p.mask ? launch_tc_bwd_t<DD, BF, DR, true, 0>(p, stream)             \
-                             : launch_tc_bwd_t<DD, BF, DR, false, 0>(p, stream)))
+  (p.mask ? ((p.deterministic || mask_tma_ok(p)) ? launch_det<DD, BF, DR, true>(p, stream)   \
+                                                 : launch_tc_bwd_t<DD, BF, DR, true, 0>(p, stream)) \
+          : p.deterministic ? launch_det<DD, BF, DR, false>(p, stream)                     \
+                            : launch_tc_bwd_t<DD, BF, DR, false, 0>(p, stream))
 #define FA_DISPATCH(DD)                                                                          \
   if (p.is_bf16) return drop ? FA_MASKED(DD, true, true)                          \
                              : FA_MASKED(DD, true, false);                        \
