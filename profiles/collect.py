@@ -18,8 +18,16 @@ if all(os.path.exists(f) for f in tl):
     with open(os.path.join(P, f"{tag}_bwd_timelines.log"), "w") as fh:
         fh.write("=== backward, no dropout\n" + open(tl[2]).read() + "=== backward, dropout 0.1\n" + open(tl[3]).read())
 rep = os.path.join(G, "prof_fwd_bwd.ncu-rep")
-if os.path.exists(rep):
-    txt = subprocess.run([sys.executable, os.path.join(P, "summarize.py"), rep], capture_output=True, text=True).stdout
+pre = os.path.join(G, "c3_fwd_bwd_ncu.txt")          # summarised on the GPU box already (the reports exceed gpurun's copy-back limit)
+for src, dst in (("wide_bench.log", "wide_bwd_bench.log"), ("det_bench.log", "det_bench.log"), ("wide_det_ncu.txt", "wide_det_ncu.txt"),
+                 ("c3_fwd_bwd_stalls.txt", "c3_fwd_bwd_stalls.txt"), ("parity_errors.log", "parity_errors.log")):
+    if os.path.exists(os.path.join(G, src)):
+        shutil.copy(os.path.join(G, src), os.path.join(P, f"{tag}_{dst}"))
+if os.path.exists(rep) or os.path.exists(pre):
+    if os.path.exists(rep):
+        txt = subprocess.run([sys.executable, os.path.join(P, "summarize.py"), rep], capture_output=True, text=True).stdout
+    else:
+        txt = open(pre).read()
     open(os.path.join(P, f"{tag}_c3_fwd_bwd_ncu.txt"), "w").write(txt)
     traffic, cur = {}, None
     for line in txt.splitlines():

@@ -119,3 +119,28 @@ def test_own_header_is_valid_c_and_links(built_lib, tmp_path):
                     "-o", str(exe), built_lib, "-Wl,-rpath," + os.path.dirname(built_lib)], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines()
     assert out[0] == "hello 6" and out[1].startswith("0 flash_attn_fwd")
+
+
+def test_ring_entry_points_validate_without_gpu(built_lib):
+    """flash_attn_b200_ring_* (include/flash_attn_b200_ext.h): workspace sizes are plain arithmetic, and bad arguments
+    come back as false + message before any CUDA or NCCL call."""
+    l = ctypes.CDLL(built_lib)
+    l.flash_attn_error.restype = ctypes.c_char_p
+    for name in ("fwd", "bwd"):
+        f = getattr(l, f"flash_attn_b200_ring_{name}_workspace_bytes")
+        f.argtypes = [ctypes.c_int] * 6
+        f.restype = ctypes.c_size_t
+    b, s, h, hk, d = 1, 16384, 32, 8, 128
+    kv = 2 * b * s * hk * d * 2
+    one = b * s * h * d * 2 + b * h * s * 4
+    assert l.flash_attn_b200_ring_fwd_workspace_bytes(1, b, s, h, hk, d) == one          # no exchange buffers alone
+    assert l.flash_attn_b200_ring_fwd_workspace_bytes(8, b, s, h, hk, d) == 2 * kv + 8 * one
+    assert l.flash_attn_b200_ring_bwd_workspace_bytes(8, b, s, h, hk, d) > l.flash_attn_b200_ring_bwd_workspace_bytes(1, b, s, h, hk, d)
+    l.flash_attn_b200_ring_comm_create.restype = ctypes.c_bool
+    comm = ctypes.c_void_p()
+    assert l.flash_attn_b200_ring_comm_create(None, 2, 5, ctypes.byref(comm)) is False     # rank out of range
+    assert b"bad argument" in l.flash_attn_error()
+    assert l.flash_attn_b200_ring_comm_create(None, 64, 0, ctypes.byref(comm)) is False    # more ranks than the ring supports
+    l.flash_attn_b200_ring_fwd.restype = ctypes.c_bool
+    assert l.flash_attn_b200_ring_fwd(None, *([None] * 7), 1, 128, 2, 2, 64, ctypes.c_float(0.125), True, True, None) is False
+    assert b"comm is NULL" in l.flash_attn_error()
