@@ -20,7 +20,7 @@ ncu --set full --clock-control none --import-source on -k regex:'tc_fwd_kernel|t
 tail -3 gpurun_out/ncu_full.log
 # the reports together exceed what gpurun copies back (64 MiB): summarise on the box, keep the text and the stall table
 python profiles/summarize.py gpurun_out/prof_fwd_bwd.ncu-rep > gpurun_out/c3_fwd_bwd_ncu.txt 2>&1
-python profiles/top_stalls.py gpurun_out/prof_fwd_bwd.ncu-rep > gpurun_out/c3_fwd_bwd_stalls.txt 2>&1
+
 rm -f gpurun_out/prof_fwd_bwd.ncu-rep
 python tests/cuda/prof_case2.py > gpurun_out/plain_prof2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'tc_bwd_wide_kernel|tc_bwd_kernel' -s 3 -c 3 \
