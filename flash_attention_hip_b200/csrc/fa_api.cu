@@ -152,8 +152,8 @@ bool bwd_impl(const char *fn, const void *dout, const void *q, const void *k, co
     return fail("%s: tcgen05 path requested but this problem is outside it", fn);
   const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
   // softmax_d; the tcgen05 backward's dq_accum is zeroed by the same kernel
-  // (num_splits == 1 on the tcgen05 path writes dq without the scratch: nothing to zero)
-  const bool zero_acc = use_tc && !p.deterministic;
+  // (the two-launch backward -- num_splits == 1, attn_mask -- writes dq without the scratch: nothing to zero)
+  const bool zero_acc = use_tc && fa::tc_bwd_uses_scratch(p);
   const char *err = fa::launch_bwd_preprocess(p, st, zero_acc ? p.dq_accum : nullptr, zero_acc ? fa::tc_bwd_scratch_floats(p) : 0);
   if (!err) err = use_tc ? fa::launch_tc_bwd(p, st) : fa::launch_generic_bwd(p, st);
   if (err) return fail("%s: %s", fn, err);

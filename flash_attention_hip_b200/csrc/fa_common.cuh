@@ -166,6 +166,7 @@ const char *launch_generic_bwd(const Params &p, cudaStream_t stream);
 const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream, float *zero_acc, long long zero_floats);
 // floats of dq_accum the tcgen05 backward uses: [b][h][query tiles][ceil(d/32)][128][32]
 long long tc_bwd_scratch_floats(const Params &p);
+bool tc_bwd_uses_scratch(const Params &p);
 // all-shapes backward on warp-level MMAs (fa_mma_bwd.cu); what launch_generic_bwd runs
 const char *launch_mma_bwd(const Params &p, cudaStream_t stream);
 

@@ -1021,6 +1021,13 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 #endif
 }
 
+// Whether launch_tc_bwd will add dQ tiles into dq_accum (then the preprocess kernel must zero it): the two-launch
+// backward (num_splits == 1, attn_mask with TMA-able rows; head sizes up to 128) never touches the scratch.
+bool tc_bwd_uses_scratch(const Params &p) {
+  if (p.d > 128) return true;
+  return !(p.deterministic || (p.mask && mask_tma_ok(p)));
+}
+
 long long tc_bwd_scratch_floats(const Params &p) {
   return (long long)p.b * p.h * ((p.sq + kT - 1) / kT) * kT * ((p.d + 31) / 32) * 32;
 }
