@@ -366,8 +366,7 @@ def run_ours(args, rank, local_rank, world):
         e1.record()
         t_host1 = time.time()
         sync_all()
-        gc.enable()
-        sampler.t_end = time.time()
+        sampler.t_end = time.time()          # (the collector stays off for the other timed loops; each collects first)
         steps_ms = [(e0 if i_ == 0 else marks[i_ - 1]).elapsed_time(marks[i_]) for i_ in range(args.steps)]
         return e0.elapsed_time(e1), steps_ms, (t_host1 - t_host0) * 1e3, w.launches, sampler.summary()
 
@@ -388,6 +387,7 @@ def run_ours(args, rank, local_rank, world):
     def time_loop(fn, n, repeats=3):
         # median of `repeats` back-to-back groups: one group now and then catches a host-side stall
         got = []
+        gc.collect()
         for _ in range(repeats):
             a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
@@ -407,6 +407,7 @@ def run_ours(args, rank, local_rank, world):
     sustained = None
     if not args.no_sustained:
         n_s = max(args.steps, int(args.sustain_seconds * 1e3 / max(ms / args.steps, 1e-3)) + 1)
+        gc.collect()
         sync_all()
         a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_s0 = time.time()
@@ -428,6 +429,7 @@ def run_ours(args, rank, local_rank, world):
         ws = Workload(torch, api, dev, count, first, 2)      # (rank-local random data; only the shapes matter)
         for _ in range(5):
             ws.step()
+        gc.collect()
         sync_all()
         a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
@@ -466,6 +468,7 @@ def run_ours(args, rank, local_rank, world):
 
         def time_e2e(fn):
             fn()
+            gc.collect()
             sync_all()
             a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
