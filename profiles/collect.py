@@ -56,7 +56,7 @@ txt = subprocess.run([sys.executable, os.path.join(P, "sass_summary.py")], captu
 open(os.path.join(P, f"{tag}_sass_summary.txt"), "w").write(txt)
 objdir = os.path.join(ROOT, "flash_attention_hip_b200", "lib", "obj")
 for name, obj, pat in (("tc_fwd_d128_bf16_dropout", "fa_tc_fwd.o", "tc_fwd_kernelILi128ELb1ELb1ELb0"),
-                       ("tc_bwd_d128_bf16_dropout", "fa_tc_bwd.o", "tc_bwd_kernelILi128ELb1ELb1ELb0ELb0")):
+                       ("tc_bwd_d128_bf16_dropout", "fa_tc_bwd.o", "tc_bwd_kernelILi128ELb1ELb1ELb0ELi0")):
     sass = subprocess.run(["cuobjdump", "-sass", os.path.join(objdir, obj)], capture_output=True, text=True).stdout
     out, on = [], False
     for line in sass.splitlines():
