@@ -974,7 +974,7 @@ const char *launch_tc_bwd_t(const Params &p, cudaStream_t stream) {
   CUtensorMap tbias = tq;    // (a valid map either way; only read when mask_tma is set)
   a.mask_tma = 0;
   if (kMask && kMode == 1 && mask_tma_ok(p)) {
-    if ((e = make_tmap_bias(&tbias, p.mask, kBF16, (uint64_t)p.mask_sk, (uint64_t)p.mask_sq, (uint64_t)p.mask_h, (uint64_t)p.mask_b, kT)))
+    if ((e = make_tmap_bias(&tbias, p.mask, kBF16, (uint64_t)p.mask_sk, (uint64_t)p.mask_sq, (uint64_t)p.mask_h, (uint64_t)p.mask_b, kT, kT)))
       return e;
     a.mask_tma = 1;
   }
@@ -1024,7 +1024,7 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 // Whether launch_tc_bwd will add dQ tiles into dq_accum (then the preprocess kernel must zero it): the two-launch
 // backward (num_splits == 1, attn_mask with TMA-able rows; head sizes up to 128) never touches the scratch.
 bool tc_bwd_uses_scratch(const Params &p) {
-  if (p.d > 128) return true;
+  if (p.d > 128) return !(p.deterministic || p.mask);      // (wide heads: attn_mask always takes the two launches)
   return !(p.deterministic || (p.mask && mask_tma_ok(p)));
 }
 
@@ -1034,7 +1034,6 @@ long long tc_bwd_scratch_floats(const Params &p) {
 
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
-  if (p.d > 128 && (p.mask || p.deterministic)) return false;   // fa_tc_bwd_wide.cu offers neither
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
   if (!p.dq_accum) return false;

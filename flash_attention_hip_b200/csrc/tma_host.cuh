@@ -67,15 +67,15 @@ inline const char *make_tmap_strided(CUtensorMap *m, const void *base, bool is_b
 }
 
 // Additive bias [batches, heads, rows, cols] (16-bit, cols contiguous) as a 4-D map (cols, rows, heads, batches) with a
-// box of box x box elements, NOT swizzled: a tile lands in shared memory as box rows of box * 2 bytes.
+// box of box_cols x box_rows elements, NOT swizzled: a tile lands in shared memory as box_rows rows of box_cols * 2 bytes.
 // cols * 2 bytes and the base must be multiples of 16 (the caller checks).
 inline const char *make_tmap_bias(CUtensorMap *m, const void *base, bool is_bf16, uint64_t cols, uint64_t rows,
-                                  uint64_t heads, uint64_t batches, int box) {
+                                  uint64_t heads, uint64_t batches, int box_cols, int box_rows) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return "cuTensorMapEncodeTiled is unavailable (driver too old?)";
   const cuuint64_t dims[4] = {cols, rows, heads ? heads : 1, batches ? batches : 1};
   const cuuint64_t strides[3] = {cols * 2, rows * cols * 2, (heads ? heads : 1) * rows * cols * 2};
-  const cuuint32_t bx[4] = {(cuuint32_t)box, (cuuint32_t)box, 1, 1};
+  const cuuint32_t bx[4] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1, 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
                          const_cast<void *>(base), dims, strides, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

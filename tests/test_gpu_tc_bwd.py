@@ -92,7 +92,11 @@ def test_tc_fwd_bwd_chain():
                                   "d96_causal_gqa", "c2_small_b2h4s2048d128", "sq_gt_sk_causal_empty_rows",
                                   "tiny_5x700_causal", "fp16_d64", "many_items_b10h8s1024d64",
                                   "many_items_gqa_s1152d128", "many_items_ragged_full", "det_full_s1024_gqa",
-                                  "det_full_sq_lt_sk", "det_full_sq_gt_sk"])
+                                  "det_full_sq_lt_sk", "det_full_sq_gt_sk",
+                                  # head sizes above 128: the two-launch pair of fa_tc_bwd_wide.cu
+                                  "d256_s128", "d256_causal", "d256_ragged_gqa", "d256_causal_gqa_drop", "d192_dropout",
+                                  "d160_sq_gt_sk_causal_fp16", "d136_sq_gt_sk_causal", "d224_tiny_5x700", "d256_packed",
+                                  "d200_packed_sq_ne_sk", "d256_many_items", "d192_many_items_packed"])
 def test_tc_bwd_deterministic_is_bit_reproducible_and_correct(name):
     """num_splits == 1 (reference flash_attn.h:94): key tiles add into dQ in a fixed order, so two runs
     agree bit for bit; the result stays within the parity tolerance."""

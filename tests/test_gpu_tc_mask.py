@@ -33,6 +33,12 @@ CASES = {
     # several KV tiles and items per CTA: the bias tile borrows the epilogue's staging block (forward), prefetch in the backward
     "many_tiles_bh": (lambda: cases.dense(3, 700, 1024, 4, 2, 128, is_causal=True), 3, 4, None, 0),
     "many_items_b1h1": (lambda: cases.dense(24, 520, 520, 8, 8, 64), 1, 1, None, 0),
+    # head sizes above 128: forward on the D = 256 build, backward as the two-launch pair of fa_tc_bwd_wide.cu
+    "d256_bh_causal": (lambda: cases.dense(2, 300, 300, 4, 2, 256, is_causal=True), 2, 4, None, 0),
+    "d192_b1h1_ragged": (lambda: cases.dense(2, 200, 328, 2, 2, 192), 1, 1, None, 0),
+    "d256_padding_minus_inf_dropout": (lambda: cases.dense(1, 257, 384, 2, 1, 256, p_dropout=0.2, seed=4, offset=6), 1, 2, 300, -np.inf),
+    "d160_sk_not_multiple_of_8_fp16": (lambda: cases.dense(1, 130, 203, 2, 1, 160, is_causal=True, is_bf16=False), 1, 2, None, 0),
+    "d256_many_items": (lambda: cases.dense(10, 520, 520, 8, 4, 256), 1, 1, None, 0),
 }
 
 
@@ -111,6 +117,8 @@ PACKED = {
     "broadcast_b1h1_dropout": ([256, 384, 130], [256, 384, 130], 4, 4, 128, dict(p_dropout=0.15, seed=3, offset=8), 1, 1, False),
     "key_padding_minus_inf_fp16": ([1024, 700, 256], [1024, 700, 256], 4, 1, 64, dict(is_bf16=False), 3, 1, True),
     "many_items": ([520] * 40, [520] * 40, 8, 8, 64, dict(is_causal=True), 1, 8, False),
+    "wide_d256_causal": ([300, 128, 417], [300, 128, 417], 4, 2, 256, dict(is_causal=True), 3, 1, False),
+    "wide_d192_cross": ([200, 77, 340], [328, 212, 130], 2, 2, 192, dict(p_dropout=0.1, seed=2, offset=3), 1, 2, False),
 }
 
 
@@ -160,7 +168,8 @@ def test_packed_mask_equals_dense_mask_per_sequence():
 
 
 @pytest.mark.parametrize("name", ["bh_d128", "b1_h1_broadcast_causal", "b_h1_d64_ragged", "padding_minus_inf", "sk_not_multiple_of_8",
-                                  "dropout_and_mask", "many_tiles_bh", "packed:mix_d128_causal", "packed:cross_d64_bh"])
+                                  "dropout_and_mask", "many_tiles_bh", "packed:mix_d128_causal", "packed:cross_d64_bh",
+                                  "d256_bh_causal", "d192_b1h1_ragged", "d160_sk_not_multiple_of_8_fp16", "packed:wide_d256_causal"])
 def test_tc_attn_mask_deterministic_bwd(name):
     """attn_mask together with num_splits == 1: the two-launch deterministic backward (dK/dV, then the mirrored dQ pass,
     which reads the bias row-wise) on the tcgen05 kernels: bit-reproducible and within the parity tolerance."""
