@@ -222,7 +222,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::mbar_init(B.q_empty, 1);     ptx::mbar_init(B.q_empty + 8, 1);
     ptx::mbar_init(B.do_full, 1);     ptx::mbar_init(B.do_empty, 1);
     ptx::mbar_init(B.s_full, 1);      ptx::mbar_init(B.dp_full, 1);
-    ptx::mbar_init(B.p_ready, 256);   ptx::mbar_init(B.ds_ready, 256);
+    ptx::mbar_init(B.p_ready, kMirror ? 384 : 256);   ptx::mbar_init(B.ds_ready, kMirror ? 384 : 256);   // mirrored: 12 warps
     ptx::mbar_init(B.dq_full, 1);     ptx::mbar_init(B.dq_drained, 128);
     ptx::mbar_init(B.acc_done, 1);
     ptx::mbar_init(B.epi_tmem_free, 128);  ptx::mbar_init(B.epi_smem_free, 1);   // (epi_smem_free: bias tiles only)
@@ -258,6 +258,137 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     ptx::mbar_arrive(B.sched_empty + 8 * slot);
     return L;
   };
+  // ---- mirrored dQ pass (mode 2): one item's score work on the NC key columns [c0, c0 + NC) of every step.
+  // TWELVE warps share a step's 128 columns 48 / 48 / 32: the eight compute warps and the four drain warps, which have
+  // nothing to drain in this mode (under ncu the pass ran at 59 % tensor-pipe activity on eight: bound by exactly this work).
+  // A lane owns one QUERY row: LSE / D are two scalars, the causal mask and the Philox calls are the forward's row-wise ones.
+  auto mirror_item = [&](auto nc_tag, const int c0, const Item &I, const int g0) {
+    constexpr int NC = decltype(nc_tag)::value;
+    static_assert(NC == 48 || NC == 32, "column split of the mirrored pass");
+    FA_ITEM_LOCALS(I);
+    const int n = (warp & 3) * 32 + lane;              // query row inside the tile == TMEM lane
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    const float c2 = a.scale_log2;
+    uint32_t add7 = 0;
+    bool t_msb = false;
+    if constexpr (kDropout) {
+      add7 = (0x80u - (a.drop_threshold & 0x7fu)) * 0x01010101u;
+      t_msb = a.drop_threshold >= 128u;
+    }
+    const int n_abs = j * kT + n;
+    const bool row_ok = n_abs < sq;
+    float nl_mine = -INFINITY, nd_mine = 0.f;          // -LSE log2 e (-inf past the end => P = 0), -D (1 - p)
+    if (row_ok) {
+      nl_mine = -a.lse[((size_t)bidx * a.h + hk) * a.sq + n_abs] * kLog2e;
+      nd_mine = -a.softmax_d[((size_t)bidx * a.h + hk) * a.sq_rounded + n_abs] * a.keep_prob;
+    }
+    const uint32_t bh = (uint32_t)((a.batch_base + bidx) * a.h + hk);
+    for (int it = 0; it < n_it; ++it) {
+      const int i = it, g = g0 + it;
+      const int k_base = i * kT + c0;                  // my first key column
+      uint32_t keep[2] = {0xffffffffu, 0xffffffffu};   // bit t of word t / 32: keep(my row, key k_base + t)
+      if constexpr (kDropout) {
+        keep[0] = 0; keep[1] = 0;
+#pragma unroll
+        for (int blk = 0; blk < NC / 16; ++blk) {
+          const fa_philox4_t rnd = fa_philox4x32((uint32_t)n_abs, (uint32_t)((k_base + 16 * blk) >> 4), bh, a.ctr3, a.key0, a.key1);
+          keep[blk / 2] |= keep_bits16(rnd, add7, t_msb) << (16 * (blk & 1));
+        }
+      }
+      uint16_t mbias[kMask ? NC : 1];
+      if constexpr (kMask) {                           // my row's NC bias values: contiguous bytes
+        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
+            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hk)) * a.mask_sq + n_abs) * (size_t)a.mask_sk + k_base;
+        const bool fast = row_ok && k_base + NC <= sk && a.mask_sk % 8 == 0 && (reinterpret_cast<uintptr_t>(a.mask) & 15) == 0;
+        if (fast) {
+#pragma unroll
+          for (int v8 = 0; v8 < NC / 8; ++v8) {
+            const uint4 x = __ldg(reinterpret_cast<const uint4 *>(mp) + v8);
+            const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) mbias[8 * v8 + e] = (uint16_t)(w4[e / 2] >> (16 * (e & 1)));
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < NC; ++c) mbias[c] = (row_ok && k_base + c < sk) ? __ldg(mp + c) : (uint16_t)0;
+        }
+      }
+      ptx::mbar_wait(B.s_full, g & 1);
+      ptx::tc_fence_after();
+      float p[NC];
+      {
+        uint32_t(&r0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&p[0]);
+        ptx::tmem_ld_x32(tS + lane_sel + c0, r0);
+        if constexpr (NC == 48) {
+          uint32_t(&r1)[16] = *reinterpret_cast<uint32_t(*)[16]>(&p[32]);
+          ptx::tmem_ld_x16(tS + lane_sel + c0 + 32, r1);
+        }
+        ptx::tmem_wait_ld();
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.p_ready);                     // S is in registers: S(it + 1) may overwrite it
+      float cs = c2;
+      if constexpr (kMask) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const uint16_t mb = mbias[c];
+          const float bias = kBF16 ? __uint_as_float((uint32_t)mb << 16) : __half2float(*reinterpret_cast<const __half *>(&mb));
+          p[c] = fmaf(p[c], c2, bias * kLog2e);
+        }
+        cs = 1.f;
+      }
+      const float2 c2v = make_float2(cs, cs), nlv = make_float2(nl_mine, nl_mine);
+#pragma unroll
+      for (int c = 0; c < NC; c += 2) {
+        const float2 x = __ffma2_rn(make_float2(p[c], p[c + 1]), c2v, nlv);
+        p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
+      }
+      const bool diag = a.causal && (k_base + NC - 1 > j * kT + shift);   // warp-uniform: some key past the tile's first row's limit
+      if (diag || k_base + NC > sk) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+          if (k_base + c >= sk || (diag && k_base + c > n_abs + shift)) p[c] = 0.f;
+      }
+      ptx::mbar_wait(B.dp_full, g & 1);
+      if (g > 0) ptx::mbar_wait(B.q_empty + 8 * ((g - 1) & 1), ((g - 1) >> 1) & 1);   // (4) of it - 1 has read dS
+      ptx::tc_fence_after();
+      {
+        const float2 ndv = make_float2(nd_mine, nd_mine);
+        uint32_t dpb[2][16];
+        ptx::tmem_ld_x16(tDP + lane_sel + c0, dpb[0]);
+        ptx::tmem_wait_ld();
+#pragma unroll
+        for (int q4 = 0; q4 < NC / 16; ++q4) {
+          uint32_t(&dp)[16] = dpb[q4 & 1];
+          if (q4 + 1 < NC / 16) ptx::tmem_ld_x16(tDP + lane_sel + c0 + (q4 + 1) * 16, dpb[(q4 + 1) & 1]);
+          uint32_t ds[8];
+#pragma unroll
+          for (int c = 0; c < 16; c += 2) {
+            const int cq = q4 * 16 + c;
+            float2 gg = ptx::u2f2(dp[c], dp[c + 1]);
+            if constexpr (kDropout) {
+              const uint32_t kb = keep[cq / 32] >> (cq % 32);
+              gg.x = (kb & 1u) ? gg.x : 0.f;
+              gg.y = (kb & 2u) ? gg.y : 0.f;
+            }
+            const float2 e = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(gg, ndv));
+            ds[c / 2] = pack2(e.x, e.y, kBF16);
+          }
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {                // logical 16-byte chunk (8 keys) of my row of dS [128 q][128 keys]
+            const int idx = (c0 + q4 * 16) / 8 + k;
+            st_shared_v4(sbase + C::kDS + (idx / 8) * C::kSub + n * 128 + (((idx % 8) ^ (n & 7)) << 4),
+                         ds[4 * k], ds[4 * k + 1], ds[4 * k + 2], ds[4 * k + 3]);
+          }
+          if (q4 + 1 < NC / 16) ptx::tmem_wait_ld();
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.ds_ready);
+    }
+  };
+
   if (warp >= 8 && warp < 12) {
     // =========================== producer warpgroup ======================================
     ptx::setmaxnreg_dec<32>();
@@ -354,6 +485,9 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
             ptx::tma_load_4d(sbase + C::kDO + c * C::kSub, str_b, B.do_full, c * 64, str_head, str_row0 + i * kT, bcoord);
         }
       }
+      if constexpr (kBiasTma) {      // (every phase of epi_smem_free is waited for, in order: an item without steps has no first bias load to do it)
+        if (a.mask_tma && n_it == 0 && nv >= 1) ptx::mbar_wait(B.epi_smem_free, (nv - 1) & 1);
+      }
       g0 += n_it;
       ++nv;
       }   // items
@@ -384,6 +518,11 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       FA_ITEM_LOCALS(I);
       ptx::mbar_wait(B.kv_full, nv & 1);
       ptx::tc_fence_after();
+      // An item without steps (mirrored pass: a query tile that sees no key) commits acc_done at once.  The drain warps wait
+      // for acc_done by PARITY: were this warp to run two items ahead of them, they would wait for the wrong phase (seen as a
+      // hang on a packed causal batch with sk << sq: runs of such items).  So an empty item first waits for the previous
+      // item's epilogue, which a non-empty one does before its first accumulating MMA anyway.
+      if (n_it == 0 && nv >= 1) ptx::mbar_wait(B.epi_tmem_free, (nv - 1) & 1);
       if (n_it > 0) {
         ptx::mbar_wait(B.q_full + 8 * (g0 & 1), (g0 >> 1) & 1);
         ptx::tc_fence_after();
@@ -483,6 +622,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       mapped_b = bidx;
       set ^= 1;
     }
+    if constexpr (kMirror) mirror_item(std::integral_constant<int, 32>{}, 96, I, g0);   // my share of the score work
     for (int it = 0; kMode == 0 && it < n_it; ++it) {
       const int hq = hk * group + it / n_i, i = q_tile_of(it);
       // dq_accum layout: [b][h][query tile][D/32][128 rows][32 floats], 16-byte chunks XOR-swizzled by row
@@ -613,32 +753,23 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
     if (L < 0) break;
     const Item I = decode(L);
     if (!I.valid) continue;
-    FA_ITEM_LOCALS(I);
-    const int n_abs = j * kT + n;                      // my key -- mirrored: my QUERY row
-    const bool kv_valid = n_abs < (kMirror ? sq : sk);
-    const bool ragged_k = j * kT + kT > sk;            // this item's key tile runs past the sequence end
-    // mirrored: LSE / D of my own row, negated and scaled like the staged vectors of the other modes
-    float nl_mine = -INFINITY, nd_mine = 0.f;
-    if constexpr (kMirror) {
-      if (kv_valid) {
-        nl_mine = -a.lse[((size_t)bidx * a.h + hk) * a.sq + n_abs] * kLog2e;
-        nd_mine = -a.softmax_d[((size_t)bidx * a.h + hk) * a.sq_rounded + n_abs] * a.keep_prob;
-      }
+    if constexpr (kMirror) {                           // the mirrored pass: columns [0, 48) and [48, 96) (the drain warps take the rest)
+      mirror_item(std::integral_constant<int, 48>{}, w * 48, I, g0);
+      g0 += I.n_it;
+      continue;
     }
+    FA_ITEM_LOCALS(I);
+    const int n_abs = j * kT + n;
+    const bool kv_valid = n_abs < sk;
+    const bool ragged_k = j * kT + kT > sk;            // this item's key tile runs past the sequence end
     uint32_t pc[4][4];
     auto ctr_init = [&](int it_) {
       const int hq_ = hk * group + it_ / n_i, i_ = q_tile_of(it_);
       const uint32_t bh_ = (uint32_t)((a.batch_base + bidx) * a.h + hq_);
 #pragma unroll
       for (int blk = 0; blk < 4; ++blk) {
-        if constexpr (kMirror) {       // my row, the four 16-key blocks of my 64 columns: the forward's own mapping
-          pc[blk][0] = (uint32_t)n_abs;
-          pc[blk][1] = (uint32_t)((i_ * kT + w * 64 + blk * 16) >> 4);
-        } else {
-          pc[blk][0] = (uint32_t)(i_ * kT + w * 64 + blk * 16 + (lane & 15));
-          pc[blk][1] = (uint32_t)(n_abs >> 4);
-        }
-        pc[blk][2] = bh_; pc[blk][3] = a.ctr3;
+        pc[blk][0] = (uint32_t)(i_ * kT + w * 64 + blk * 16 + (lane & 15));
+        pc[blk][1] = (uint32_t)(n_abs >> 4); pc[blk][2] = bh_; pc[blk][3] = a.ctr3;
       }
     };
     if constexpr (kDropout) {
@@ -676,12 +807,10 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
         // 16x16 bit transposes inside each half-warp (four at once, two per word): butterfly over
         // lane bits 8, 4, 2, 1 -- 8 shuffles instead of the 64 a gather per (query, key) pair costs
-        if constexpr (!kMirror) {           // (mirrored: the words already are my row's keep bits, column by column)
-          bit_transpose_stage<8>(w01, w23, lane);
-          bit_transpose_stage<4>(w01, w23, lane);
-          bit_transpose_stage<2>(w01, w23, lane);
-          bit_transpose_stage<1>(w01, w23, lane);
-        }
+        bit_transpose_stage<8>(w01, w23, lane);
+        bit_transpose_stage<4>(w01, w23, lane);
+        bit_transpose_stage<2>(w01, w23, lane);
+        bit_transpose_stage<1>(w01, w23, lane);
         keep_lo = w01;                    // bit t: keep(query q_base + t, my key)
         keep_hi = w23;
       }
@@ -690,24 +819,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       // depend on S^T either -- fetched before the wait for it, so the loads' latency is spent waiting anyway
       // (lanes hold consecutive keys: each load instruction reads 64 contiguous bytes of one mask row)
       uint16_t mbias[kMask ? 64 : 1];
-      if constexpr (kMask && kMirror) {
-        // mirrored: my row's 64 bias values are 128 contiguous bytes (columns = keys q_base .. q_base + 63)
-        const uint16_t *mp = static_cast<const uint16_t *>(a.mask) +
-            (((size_t)(a.mask_b == 1 ? 0 : bidx) * a.mask_h + (a.mask_h == 1 ? 0 : hq)) * a.mask_sq + n_abs) * (size_t)a.mask_sk + q_base;
-        const bool fast = kv_valid && q_base + 64 <= sk && a.mask_sk % 8 == 0 && (reinterpret_cast<uintptr_t>(a.mask) & 15) == 0;
-        if (fast) {
-#pragma unroll
-          for (int v8 = 0; v8 < 8; ++v8) {
-            const uint4 x = __ldg(reinterpret_cast<const uint4 *>(mp) + v8);
-            const uint32_t w4[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) mbias[8 * v8 + e] = (uint16_t)(w4[e / 2] >> (16 * (e & 1)));
-          }
-        } else {
-#pragma unroll
-          for (int c = 0; c < 64; ++c) mbias[c] = (kv_valid && q_base + c < sk) ? __ldg(mp + c) : (uint16_t)0;
-        }
-      } else if (kBiasTma && a.mask_tma) {
+      if (kBiasTma && a.mask_tma) {
         ptx::mbar_wait(B.bias_full, g & 1);
         const uint16_t *bt = reinterpret_cast<const uint16_t *>(smem_raw + C::kDQ) + (size_t)(w * 64) * kT + n;   // [query][key]
         const bool rows_ragged = q_base + 64 > sq;         // warp-uniform
@@ -738,14 +850,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_wait_ld();
       }
       FA_TRACE_EV(trc, 30);
-      if constexpr (kMirror) {              // S is in registers and nothing is written back: S(it + 1) may overwrite it
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(B.p_ready);
-      }
-      // causal, fused / dK-dV: my key n_abs is visible to query q iff q >= lim; mirrored: my row sees key k iff k <= -lim
-      const bool diag = a.causal && (kMirror ? (q_base + 63 > j * kT + shift) : (j * kT + kT - 1 > q_base + shift));   // warp-uniform
-      const int lim = kMirror ? -(n_abs + shift) : n_abs - shift;
-      const bool ragged = kMirror ? (i * kT + kT > sk) : ragged_k;
+      const bool diag = a.causal && (j * kT + kT - 1 > q_base + shift);   // warp-uniform
+      const int lim = n_abs - shift;                     // causal: visible iff q >= lim
       float cs = c2;
       if constexpr (kMask) {                                      // s <- s * scale_log2 + bias * log2 e
 #pragma unroll
@@ -760,8 +866,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
       if constexpr (kDropout) ctr_init(it + 1);           // (one wasted draw after the last iteration)
 #pragma unroll
       for (int c = 0; c < 64; c += 4) {
-        const float4 nl = kMirror ? make_float4(nl_mine, nl_mine, nl_mine, nl_mine)
-                                  : ld_shared_f32x4(stat + 4 * c);        // -lse2 of 4 query columns
+        const float4 nl = ld_shared_f32x4(stat + 4 * c);                  // -lse2 of 4 query columns
         float2 x = __ffma2_rn(make_float2(p[c], p[c + 1]), c2v, make_float2(nl.x, nl.y));
         float2 y = __ffma2_rn(make_float2(p[c + 2], p[c + 3]), c2v, make_float2(nl.z, nl.w));
         p[c] = ptx::ex2(x.x); p[c + 1] = ptx::ex2(x.y);
@@ -789,17 +894,12 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         }
       }
       FA_TRACE_EV(trc, 31);
-      if (diag || ragged) {                              // CTA/warp-uniform: only diagonal and last key tiles
+      if (diag || ragged_k) {                            // CTA/warp-uniform: only diagonal and last key tiles
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
-          if constexpr (kMirror) {                       // column = key q_base + c
-            if (q_base + c >= sk || (diag && q_base + c > -lim)) p[c] = 0.f;
-          } else {
-            if (!kv_valid || (diag && q_base + c < lim)) p[c] = 0.f;
-          }
-        }
+        for (int c = 0; c < 64; ++c)
+          if (!kv_valid || (diag && q_base + c < lim)) p[c] = 0.f;
       }
-      if constexpr (!kMirror) {
+      {
         uint32_t pk[32];
 #pragma unroll
         for (int c = 0; c < 32; ++c) pk[c] = pack2(p[2 * c], p[2 * c + 1], kBF16);
@@ -818,10 +918,8 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         ptx::tmem_wait_st();
         FA_TRACE_EV(trc, 33);
       }
-      if constexpr (!kMirror) {
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(B.p_ready);
-      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(B.p_ready);
       FA_TRACE_EV(trc, 13);
 
       ptx::mbar_wait(B.dp_full, g & 1);
@@ -854,8 +952,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
               g23.x = (kb & 4u) ? g23.x : 0.f;
               g23.y = (kb & 8u) ? g23.y : 0.f;
             }
-            const float4 nd = kMirror ? make_float4(nd_mine, nd_mine, nd_mine, nd_mine)
-                                      : ld_shared_f32x4(stat + 512 + 4 * cq);   // -D of 4 query columns
+            const float4 nd = ld_shared_f32x4(stat + 512 + 4 * cq);        // -D of 4 query columns
             const float2 e01 = __fmul2_rn(make_float2(p[cq], p[cq + 1]), __fadd2_rn(g01, make_float2(nd.x, nd.y)));
             const float2 e23 = __fmul2_rn(make_float2(p[cq + 2], p[cq + 3]), __fadd2_rn(g23, make_float2(nd.z, nd.w)));
             ds[c / 2] = pack2(e01.x, e01.y, kBF16);

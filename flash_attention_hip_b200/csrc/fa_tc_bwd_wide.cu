@@ -275,6 +275,9 @@ tc_bwd_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             if (lane == 0) ptx::mbar_arrive(b_q_full);
           }
         }
+        if constexpr (kBiasTma) {    // (every phase of epi_smem_free is waited for, in order)
+          if (a.mask_tma && I.n_it == 0 && nv >= 1) ptx::mbar_wait(b_epi_smem_free, (nv - 1) & 1);
+        }
         g0 += I.n_it;
         ++nv;
       }
@@ -297,6 +300,11 @@ tc_bwd_wide_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         const uint32_t half_q = 2 * I.dh * W::kSubQ, half_k = 2 * I.dh * W::kSubK;
         ptx::mbar_wait(b_kv_full, nv & 1);
         ptx::tc_fence_after();
+        // An item without steps (mirrored pass: a query tile that sees no key) commits acc_done at once.  The drain warps wait
+        // for acc_done by PARITY: were this warp to run two items ahead of them, they would wait for the wrong phase (seen as a
+        // hang on a packed causal batch with sk << sq: runs of such items).  So an empty item first waits for the previous
+        // item's epilogue, which a non-empty one does before its first accumulating MMA anyway.
+        if (I.n_it == 0 && nv >= 1) ptx::mbar_wait(b_epi_tmem_free, (nv - 1) & 1);
         for (int it = 0; it < I.n_it; ++it) {
           const int g = g0 + it;
           const uint32_t b16 = ptx::opaque(sbase >> 4);

@@ -107,3 +107,33 @@ def test_tc_varlen_bwd_deterministic(name):
     for t in ("dq", "dk", "dv"):
         assert np.array_equal(a[t], b[t]), t
     G.check_bwd("tc_varlen_deterministic/" + name, pb, a, rb, None)
+
+
+def test_deterministic_backward_runs_of_empty_query_tiles():
+    """Packed causal sequences with far fewer keys than queries: most query tiles of such a sequence see no key, so the
+    mirrored dQ pass of the deterministic backward meets long RUNS of items without steps in its persistent queue.  Their
+    acc_done commits used to run two phases ahead of the drain warps' parity waits (a hang, once in ~10 processes, found by
+    the random sweep); repeated here with the work that made it likely (attn_mask, GQA, >148 items)."""
+    import gpu_util as G
+    lq = [308, 898, 318, 321, 700, 876, 230, 303, 892]
+    lk = [695, 745, 753, 852, 692, 17, 473, 817, 226]
+    pb = cases.varlen(lq, lk, 16, 4, 128, is_causal=True)
+    rng = np.random.default_rng(3)
+    pb.attn_mask = O.to_storage(rng.standard_normal((1, 16, pb.seqlen_q, pb.seqlen_k), dtype=np.float32), True)
+    q, k, v, dout = cases.make_inputs(pb, seed=21)
+    ref = O.forward(pb, q, k, v)
+    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    small = cases.varlen([518, 497], [497, 518], 3, 3, 16, is_causal=True)        # a few-item launch in between, as in the sweep
+    qs, ks, vs, ds_ = cases.make_inputs(small, seed=22)
+    rs = O.forward(small, qs, ks, vs)
+    first = None
+    for rep in range(12):
+        G.run_bwd(small, ds_, qs, ks, vs, rs["out"], rs["lse"], deterministic=True)
+        gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"], deterministic=True)
+        assert gb["path"] == 2
+        if first is None:
+            first = gb
+            G.check_bwd("tc_varlen_deterministic/empty_query_tile_runs", pb, gb, rb, None)
+        else:
+            for t in ("dq", "dk", "dv"):
+                assert np.array_equal(gb[t], first[t]), (rep, t)
