@@ -109,7 +109,8 @@ def test_tc_varlen_bwd_deterministic(name):
     G.check_bwd("tc_varlen_deterministic/" + name, pb, a, rb, None)
 
 
-def test_deterministic_backward_runs_of_empty_query_tiles():
+@pytest.mark.parametrize("d", [128, 256])
+def test_deterministic_backward_runs_of_empty_query_tiles(d):
     """Packed causal sequences with far fewer keys than queries: most query tiles of such a sequence see no key, so the
     mirrored dQ pass of the deterministic backward meets long RUNS of items without steps in its persistent queue.  Their
     acc_done commits used to run two phases ahead of the drain warps' parity waits (a hang, once in ~10 processes, found by
@@ -117,7 +118,7 @@ def test_deterministic_backward_runs_of_empty_query_tiles():
     import gpu_util as G
     lq = [308, 898, 318, 321, 700, 876, 230, 303, 892]
     lk = [695, 745, 753, 852, 692, 17, 473, 817, 226]
-    pb = cases.varlen(lq, lk, 16, 4, 128, is_causal=True)
+    pb = cases.varlen(lq, lk, 16, 4, d, is_causal=True)
     rng = np.random.default_rng(3)
     pb.attn_mask = O.to_storage(rng.standard_normal((1, 16, pb.seqlen_q, pb.seqlen_k), dtype=np.float32), True)
     q, k, v, dout = cases.make_inputs(pb, seed=21)
@@ -133,7 +134,7 @@ def test_deterministic_backward_runs_of_empty_query_tiles():
         assert gb["path"] == 2
         if first is None:
             first = gb
-            G.check_bwd("tc_varlen_deterministic/empty_query_tile_runs", pb, gb, rb, None)
+            G.check_bwd(f"tc_varlen_deterministic/empty_query_tile_runs_d{d}", pb, gb, rb, None)
         else:
             for t in ("dq", "dk", "dv"):
                 assert np.array_equal(gb[t], first[t]), (rep, t)
