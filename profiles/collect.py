@@ -20,7 +20,8 @@ if all(os.path.exists(f) for f in tl):
 rep = os.path.join(G, "prof_fwd_bwd.ncu-rep")
 pre = os.path.join(G, "c3_fwd_bwd_ncu.txt")          # summarised on the GPU box already (the reports exceed gpurun's copy-back limit)
 for src, dst in (("wide_bench.log", "wide_bwd_bench.log"), ("det_bench.log", "det_bench.log"), ("wide_det_ncu.txt", "wide_det_ncu.txt"),
-                 ("c3_fwd_bwd_stalls.txt", "c3_fwd_bwd_stalls.txt"), ("parity_errors.log", "parity_errors.log")):
+                 ("c3_fwd_bwd_stalls.txt", "c3_fwd_bwd_stalls.txt"), ("parity_errors.log", "parity_errors.log"),
+                 ("short_end_launches.csv", "short_end_launches.csv"), ("host_latency.log", "host_latency.log")):
     if os.path.exists(os.path.join(G, src)):
         shutil.copy(os.path.join(G, src), os.path.join(P, f"{tag}_{dst}"))
 if os.path.exists(rep) or os.path.exists(pre):

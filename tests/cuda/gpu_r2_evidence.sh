@@ -28,4 +28,8 @@ ncu --set full --clock-control none --import-source on -k regex:'tc_bwd_wide_ker
 tail -3 gpurun_out/ncu_full2.log
 python profiles/summarize.py gpurun_out/prof_wide_det.ncu-rep > gpurun_out/wide_det_ncu.txt 2>&1
 rm -f gpurun_out/prof_wide_det.ncu-rep
+python tests/cuda/short_end_case.py > gpurun_out/plain_short.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv --log-file gpurun_out/short_end_launches.csv \
+    python tests/cuda/short_end_case.py > gpurun_out/ncu_short.log 2>&1
+python tests/cuda/host_latency.py > gpurun_out/host_latency.log 2>&1; cat gpurun_out/host_latency.log
 ls -la gpurun_out/ | tail -12
