@@ -111,47 +111,46 @@ struct MergeArgs {
   int n;
 };
 
+// One warp per (batch, row, head).  Lane t holds step t's LSE for the row (+inf: the step did not cover it, or saw no key):
+// warp max / sum give the log-sum-exp weights; every lane then owns 4 output elements per 128 (8-byte loads and stores).
 template <typename T>
 __global__ void __launch_bounds__(256)
 ring_merge_kernel(const MergeArgs m, T *__restrict__ out, float *__restrict__ lse_out, int b, int s, int h, int d) {
-  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const unsigned warp = (unsigned)((blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5);   // b * s * h < 2^32 (checked by the caller)
   const int lane = threadIdx.x & 31;
-  if (warp >= (long long)b * s * h) return;
-  const int head = (int)(warp % h), row = (int)((warp / h) % s), bi = (int)(warp / ((long long)h * s));
-  float l[kMaxRanks];
-  float mx = -INFINITY;
-#pragma unroll
-  for (int t = 0; t < kMaxRanks; ++t) {
-    l[t] = INFINITY;                                     // +inf: this step saw no key for the row
-    if (t < m.n && row >= m.q0[t] && row < m.q0[t] + m.rows[t])
-      l[t] = m.lse[t][((size_t)bi * h + head) * m.rows[t] + (row - m.q0[t])];
-    if (l[t] != INFINITY) mx = fmaxf(mx, l[t]);
+  if (warp >= (unsigned)b * (unsigned)s * (unsigned)h) return;
+  const int head = (int)(warp % (unsigned)h), row = (int)((warp / (unsigned)h) % (unsigned)s), bi = (int)(warp / ((unsigned)h * (unsigned)s));
+  float l = INFINITY;
+  int rel = 0;
+  if (lane < m.n) {
+    rel = row - m.q0[lane];
+    if (rel >= 0 && rel < m.rows[lane]) l = m.lse[lane][((size_t)bi * h + head) * m.rows[lane] + rel];
   }
+  const float mx = fa::warp_max(l == INFINITY ? -INFINITY : l);
   T *dst = out + (((size_t)bi * s + row) * h + head) * d;
   if (mx == -INFINITY) {                                 // no key anywhere: out = 0, lse = +inf
-    for (int c = lane; c < d; c += 32) dst[c] = fa::from_f32<T>(0.f);
+    for (int c = lane * 4; c < d; c += 128) *reinterpret_cast<uint2 *>(dst + c) = make_uint2(0u, 0u);
     if (lane == 0) lse_out[((size_t)bi * h + head) * s + row] = INFINITY;
     return;
   }
-  float tot = 0.f;
-#pragma unroll
-  for (int t = 0; t < kMaxRanks; ++t) {
-    l[t] = l[t] == INFINITY ? 0.f : __expf(l[t] - mx);   // from here on: the step's weight, unnormalised
-    tot += l[t];
-  }
+  const float w = l == INFINITY ? 0.f : __expf(l - mx);  // my step's weight, unnormalised
+  const float tot = fa::warp_sum(w);
   const float inv = 1.f / tot;
-  for (int c = lane * 2; c < d; c += 64) {               // d is a multiple of 8: pairs never straddle the end
-    float a0 = 0.f, a1 = 0.f;
-#pragma unroll
-    for (int t = 0; t < kMaxRanks; ++t) {
-      if (t < m.n && l[t] != 0.f) {
-        const T *src = static_cast<const T *>(m.o[t]) + (((size_t)bi * m.rows[t] + (row - m.q0[t])) * h + head) * d + c;
-        a0 = fmaf(l[t], fa::to_f32<T>(src[0]), a0);
-        a1 = fmaf(l[t], fa::to_f32<T>(src[1]), a1);
+  for (int c = lane * 4; c < d; c += 128) {              // d is a multiple of 8: a lane's 4 elements never straddle the end
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (int t = 0; t < m.n; ++t) {
+      const float wt = __shfl_sync(0xffffffffu, w, t);
+      const int rt = __shfl_sync(0xffffffffu, rel, t);
+      if (wt != 0.f) {                                   // (warp-uniform)
+        const T *src = static_cast<const T *>(m.o[t]) + (((size_t)bi * m.rows[t] + rt) * h + head) * d + c;
+        const uint2 v = *reinterpret_cast<const uint2 *>(src);
+        const T *e = reinterpret_cast<const T *>(&v);
+        a0 = fmaf(wt, fa::to_f32<T>(e[0]), a0); a1 = fmaf(wt, fa::to_f32<T>(e[1]), a1);
+        a2 = fmaf(wt, fa::to_f32<T>(e[2]), a2); a3 = fmaf(wt, fa::to_f32<T>(e[3]), a3);
       }
     }
-    dst[c] = fa::from_f32<T>(a0 * inv);
-    dst[c + 1] = fa::from_f32<T>(a1 * inv);
+    T o4[4] = {fa::from_f32<T>(a0 * inv), fa::from_f32<T>(a1 * inv), fa::from_f32<T>(a2 * inv), fa::from_f32<T>(a3 * inv)};
+    *reinterpret_cast<uint2 *>(dst + c) = *reinterpret_cast<const uint2 *>(o4);
   }
   if (lane == 0) lse_out[((size_t)bi * h + head) * s + row] = mx + __logf(tot);
 }
@@ -352,6 +351,7 @@ bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, c
     }
   }
   const long long warps = (long long)b * s_local * h;
+  if (warps >= (1ll << 31)) return failf("%s: batch * s_local * heads must stay below 2^31", fn);
   const int blocks = (int)((warps * 32 + 255) / 256);
   if (is_bf16)
     ring_merge_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(m, static_cast<__nv_bfloat16 *>(out), static_cast<float *>(lse),
