@@ -87,6 +87,16 @@ def test_cp_kernels_match_torch(dtype):
     dst = torch.empty(1000, 7, device="cuda", dtype=dtype)
     api.cp_store(dst, acc)
     assert torch.equal(dst, acc.to(dtype))
+    # a length that is not a multiple of 8 (vector body + scalar tail), and buffers that are not 16-byte aligned (scalar kernels)
+    for n, off in ((3003, 0), (3003, 1), (5, 0)):
+        acc = torch.randn(n + off, device="cuda")[off:]
+        blk = torch.randn(n + off, device="cuda").to(dtype)[off:]
+        ref = acc + blk.float()
+        api.cp_accumulate(acc, blk)
+        assert torch.equal(acc, ref), (n, off)
+        dst = torch.empty(n + off, device="cuda", dtype=dtype)[off:]
+        api.cp_store(dst, acc)
+        assert torch.equal(dst, acc.to(dtype)), (n, off)
 
 
 def test_ring_world1_equals_plain_calls():
