@@ -92,7 +92,15 @@ __device__ __forceinline__ float warp_sum(float v) {
 // call -- INTEGRATION.md), so both are cached per device ordinal, lock-free (re-doing either is harmless).
 constexpr int kMaxCachedDevices = 64;
 
-// Current device and its SM count.  Returns nullptr or a static error string.
+// SMs the persistent kernels leave free (thread-local; 0 outside the ring entry points).  A persistent launch holds one
+// CTA on every SM until it is over, so a communication kernel that becomes runnable at the same moment finds no SM and
+// runs AFTER it: the ring steps leave NCCL's send / receive CTAs a few SMs instead (csrc/fa_ring.cu).
+inline int &persistent_sm_reserve() {
+  static thread_local int reserve = 0;
+  return reserve;
+}
+
+// Current device and the SM count the persistent kernels may fill.  Returns nullptr or a static error string.
 inline const char *current_device(int *dev, int *sm_count) {
   static std::atomic<int> cache[kMaxCachedDevices];     // zero-initialised
   if (cudaGetDevice(dev) != cudaSuccess) return "cudaGetDevice failed";
@@ -102,7 +110,8 @@ inline const char *current_device(int *dev, int *sm_count) {
       return "cudaDeviceGetAttribute(MultiProcessorCount) failed";
     if (*dev >= 0 && *dev < kMaxCachedDevices) cache[*dev].store(c, std::memory_order_relaxed);
   }
-  *sm_count = c;
+  const int r = persistent_sm_reserve();
+  *sm_count = (r > 0 && c - r >= 16) ? c - r : c;
   return nullptr;
 }
 

@@ -25,6 +25,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -207,6 +208,24 @@ bool exchange(const char *fn, fa_ring_comm *c, const void *src0, void *dst0, siz
 
 struct RingShape { int b, s, h, hk, d; bool bf16; };
 
+// SMs left to NCCL's send / receive kernel while a ring step's (persistent) attention kernels run.  Without them the
+// exchange of step t + 1, which becomes runnable at the same moment as the kernels of step t, finds every SM taken and
+// runs after them: measured at N = 8, S = 128k: 18.8 ms forward with no SM left free (13.5 ms of kernels + 8 x 0.66 ms of
+// exposed exchange).  FA_B200_RING_SM_RESERVE overrides the default.
+int ring_sm_reserve(int nranks) {
+  if (nranks <= 1) return 0;
+  static const int v = [] {
+    const char *e = getenv("FA_B200_RING_SM_RESERVE");
+    return e ? atoi(e) : 8;
+  }();
+  return v < 0 ? 0 : v;
+}
+struct ReserveGuard {
+  int saved;
+  explicit ReserveGuard(int r) : saved(fa::persistent_sm_reserve()) { fa::persistent_sm_reserve() = r; }
+  ~ReserveGuard() { fa::persistent_sm_reserve() = saved; }
+};
+
 bool check_shape(const char *fn, const fa_ring_comm *c, const RingShape &r, bool causal) {
   if (!c) return failf("%s: comm is NULL", fn);
   if (r.b <= 0 || r.s <= 0 || r.h <= 0 || r.hk <= 0 || r.h % r.hk) return failf("%s: bad shape", fn);
@@ -317,6 +336,7 @@ bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, c
   MergeArgs m;
   memset(&m, 0, sizeof(m));
   m.n = N;
+  const ReserveGuard reserve(ring_sm_reserve(N));
   if (N > 1) {
     FA_CUDA(cudaEventRecord(c->ev_in, st));
     FA_CUDA(cudaStreamWaitEvent(c->cs, c->ev_in, 0));
@@ -390,6 +410,7 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q
   float *softmax_d = reinterpret_cast<float *>(w); w += up256((size_t)h * s_r * 4);
   float *dq_accum = reinterpret_cast<float *>(w);
 
+  const ReserveGuard reserve(ring_sm_reserve(N));
   FA_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)b * s_local * h * d * 4, st));
   FA_CUDA(cudaMemsetAsync(D[0], 0, 2 * dkv_bytes, st));
   if (N > 1) {
@@ -408,11 +429,8 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q
     const int src = (c->rank - t + N) % N;
     const Step sp = ring_step(is_causal, c->rank, src, s_local);
     const int rows = sp.q1 - sp.q0, krows = sp.k1 - sp.k0;
-    if (t > 0) {
-      // the partial sums of the chunk held now arrive from the previous rank (sent there after its step t - 1)
-      FA_CUDA(cudaStreamWaitEvent(st, c->ev_dkv[t - 1], 0));
-      cur ^= 1;
-    }
+    if (t > 0) cur ^= 1;       // D[cur]: the sums of the chunk held now, on their way in from the previous rank
+    bool sums_here = t == 0;
     for (int bi = 0; bi < b; ++bi) {
       const size_t qoff = (((size_t)bi * s_local + sp.q0) * h) * d * 2, koff = (((size_t)bi * s_local + sp.k0) * hk) * d * 2;
       FA_CUDA(cudaMemcpy2DAsync(lse_c, (size_t)rows * 4, static_cast<const float *>(lse) + (size_t)bi * h * s_local + sp.q0,
@@ -425,6 +443,12 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q
         return false;
       FA_CALL(flash_attn_b200_cp_accumulate(dq_acc + ((size_t)bi * s_local + sp.q0) * h * d, dq_t, (int64_t)rows * h * d,
                                             is_bf16, stream));
+      if (!sums_here) {
+        // the partial sums arrive from the previous rank (sent there after its step t - 1).  Waited for HERE, not before
+        // the step's kernels: only the two additions below need them, the 134 MB transfer runs under flash_attn_bwd
+        FA_CUDA(cudaStreamWaitEvent(st, c->ev_dkv[t - 1], 0));
+        sums_here = true;
+      }
       float *dk_sum = reinterpret_cast<float *>(D[cur]) + ((size_t)bi * s_local + sp.k0) * hk * d;
       FA_CALL(flash_attn_b200_cp_accumulate(dk_sum, dk_t, (int64_t)krows * hk * d, is_bf16, stream));
       FA_CALL(flash_attn_b200_cp_accumulate(dk_sum + kv_elems, dv_t, (int64_t)krows * hk * d, is_bf16, stream));
