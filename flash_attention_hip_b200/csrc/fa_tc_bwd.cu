@@ -1,5 +1,8 @@
 // fa_tc_bwd.cu -- FlashAttention-2 backward for sm_100a (tcgen05 + TMEM + TMA).
-// Implements flash_attn_bwd (reference flash_attn.h:68-99) for head_size 64/128.
+// Implements flash_attn_bwd / flash_attn_varlen_bwd (reference flash_attn.h:68-99, :101-134) for head sizes up to 128
+// (compiled widths 64 and 128; fa_tc_bwd_wide.cu takes 136..256).  The fused kernel described here is kMode 0; num_splits == 1
+// and attn_mask run as two launches of the same kernel without atomics (kMode 1: dK / dV only, kMode 2: dQ only with the
+// operand roles mirrored -- see the comment at the kernel).
 //
 // One CTA owns one 128-key tile (K_j, V_j) of one (batch, kv head) and loops over
 // the query tiles that see it (and over the query heads of the GQA group),
@@ -148,7 +151,7 @@ tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
   // fastest (causal: the heaviest first).  Dense inputs: one persistent CTA per SM pulls items from a global
   // counter, and its TMA / MMA / drain warps run ahead into the next item while the compute warps write dK
   // and dV out (a CTA's start -- DRAM latency of the first loads -- and its 64 KB epilogue on a ~26 B/clk
-  // store port were ~8000 of ~70000 cycles per item, traced).  Packed inputs and ordered dQ: one item per CTA.
+  // store port were ~8000 of ~70000 cycles per item, traced).  Packed inputs run persistent too (tensor maps re-bounded per sequence).
   struct Item {
     int j, hk, bidx, sq, sk, qrow0, krow0, bcoord, shift, i_min, n_i, n_it;
     size_t qtok0, ktok0;
