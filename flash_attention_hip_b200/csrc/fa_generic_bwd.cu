@@ -95,6 +95,67 @@ bwd_preprocess_flat_kernel(const T *__restrict__ o, const T *__restrict__ g, flo
   }
 }
 
+// The packed counterpart (d = 64 or 128, the fused tcgen05 backward follows): dout / out are flat [token * heads][d] arrays
+// as well, only the sequence of a token has to be looked up (binary search in cu_seqlens_q: b + 1 words, cached), and
+// dq_accum is zeroed ROW BY ROW next to it -- the kLanes lanes of a row clear that row's 128-byte slices of the
+// [b][h][query tile][d / 32][128][32] scratch -- so that only rows that exist are written: the scratch is sized for
+// max_seqlen_q, and a flat clear of it cost more than the backward's main kernel on batches of short sequences
+// (128 sequences of 128 / 256 tokens: 263 of 600 us; profiles/r02m_short_end_launches.csv).  Rows past a sequence's end
+// inside its last tile keep whatever they held: the main kernel adds exact zeros to them and nothing reads them.
+template <typename T, int kLanes>
+__global__ void __launch_bounds__(256)
+bwd_preprocess_packed_kernel(const T *__restrict__ o, const T *__restrict__ g, float *__restrict__ softmax_d,
+                             const int32_t *__restrict__ cu_q, int nb, int h, int sq_rounded,
+                             float *__restrict__ acc, int nqt) {
+  constexpr int kUnroll = 4;
+  constexpr int kBlk = kLanes / 4;                       // 32-column blocks of the scratch per row (d / 32)
+  const long long rows = (long long)__ldg(cu_q + nb) * h;   // total tokens: known on the device only
+  const long long nvec = rows * kLanes;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  for (long long v0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; v0 - lane < nvec; v0 += stride * kUnroll) {
+    uint4 ro[kUnroll], rg[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      if (v < nvec) {
+        ro[u] = reinterpret_cast<const uint4 *>(o)[v];
+        rg[u] = reinterpret_cast<const uint4 *>(g)[v];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long v = v0 + u * stride;
+      float accv = 0.f;
+      if (v < nvec) {
+        const T *eo = reinterpret_cast<const T *>(&ro[u]);
+        const T *eg = reinterpret_cast<const T *>(&rg[u]);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) accv = fmaf(to_f32<T>(eo[t]), to_f32<T>(eg[t]), accv);
+      }
+#pragma unroll
+      for (int off = kLanes / 2; off > 0; off >>= 1) accv += __shfl_xor_sync(0xffffffffu, accv, off);
+      if (v < nvec) {
+        const long long r = v / kLanes;                  // (token, head) row
+        const int part = (int)(v % kLanes);
+        const int tok = (int)(r / h), head = (int)(r % h);
+        int lo = 0, hi = nb;                             // the sequence b with cu_q[b] <= tok < cu_q[b + 1]
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (__ldg(cu_q + mid) <= tok) lo = mid; else hi = mid;
+        }
+        const int row = tok - __ldg(cu_q + lo);
+        if (part == 0) softmax_d[((long long)lo * h + head) * sq_rounded + row] = accv;
+        if (acc) {                                       // my 32 bytes of the row's kBlk slices of 128 bytes
+          float *p = acc + ((((long long)lo * h + head) * nqt + (row >> 7)) * kBlk + (part >> 2)) * 4096 + (row & 127) * 32 + (part & 3) * 8;
+          reinterpret_cast<float4 *>(p)[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+          reinterpret_cast<float4 *>(p)[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+    }
+  }
+}
+
 }  // namespace
 
 const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream, float *zero_acc, long long zero_floats) {
@@ -116,6 +177,19 @@ const char *launch_bwd_preprocess(const Params &p, cudaStream_t stream, float *z
     } else {
       if (lanes == 8) FA_PRE(__half, 8); else if (lanes == 16) FA_PRE(__half, 16); else FA_PRE(__half, 32);
     }
+#undef FA_PRE
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+  }
+  if (p.cu_q && (lanes == 8 || lanes == 16)) {
+    const int grid = 148 * 8;                            // grid-stride over cu_seqlens_q[b] * heads rows (a device-side number)
+    const int nqt = (p.sq + 127) / 128;
+#define FA_PRE(T, L)                                                                                       \
+  bwd_preprocess_packed_kernel<T, L><<<grid, 256, 0, stream>>>(static_cast<const T *>(p.out),              \
+                                                               static_cast<const T *>(p.dout), p.softmax_d, \
+                                                               p.cu_q, p.b, p.h, p.sq_rounded, zero_acc, nqt)
+    if (p.is_bf16) { if (lanes == 8) FA_PRE(__nv_bfloat16, 8); else FA_PRE(__nv_bfloat16, 16); }
+    else { if (lanes == 8) FA_PRE(__half, 8); else FA_PRE(__half, 16); }
 #undef FA_PRE
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
