@@ -1123,7 +1123,15 @@ int trace_read_bwd(unsigned long long *dst, int role, int max_events) {
 
 // Whether launch_tc_bwd will add dQ tiles into dq_accum (then the preprocess kernel must zero it): the two-launch
 // backward (num_splits == 1, attn_mask with TMA-able rows; head sizes up to 128) never touches the scratch.
+// The caller's scratch pair as include/flash_attn.h sizes it: dq_accum >= b * sq_rounded * h * d_rounded floats with
+// sq_rounded a multiple of 128 and d_rounded >= head_size rounded up to 32.  A call whose scratch is smaller (or NULL)
+// still runs on the tcgen05 kernels: as the two-launch pair, which does not use dq_accum at all.
+bool scratch_fits(const Params &p) {
+  return p.dq_accum && p.sq_rounded % kT == 0 && p.sq_rounded >= p.sq && p.d_rounded >= (p.d + 31) / 32 * 32;
+}
+
 bool tc_bwd_uses_scratch(const Params &p) {
+  if (!scratch_fits(p)) return false;
   if (p.d > 128) return !(p.deterministic || p.mask);      // (wide heads: attn_mask always takes the two launches)
   return !(p.deterministic || (p.mask && mask_tma_ok(p)));
 }
@@ -1136,10 +1144,7 @@ bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
   if (!(p.scale > 0.f)) return false;
   if (p.sq <= 0 || p.sk <= 0) return false;
-  if (!p.dq_accum) return false;
-  // scratch contract (include/flash_attn.h): dq_accum >= b * sq_rounded * h * d_rounded floats
-  if (p.sq_rounded % kT || p.sq_rounded < p.sq || p.d_rounded < (p.d + 31) / 32 * 32) return false;
-  return true;
+  return true;                                          // (a scratch pair below the contract: two launches, see scratch_fits)
 }
 
 namespace {
@@ -1151,7 +1156,9 @@ const char *launch_det(const Params &p, cudaStream_t stream) {
 }
 }  // namespace
 
-const char *launch_tc_bwd(const Params &p, cudaStream_t stream) {
+const char *launch_tc_bwd(const Params &p_in, cudaStream_t stream) {
+  Params p = p_in;
+  if (!scratch_fits(p)) p.deterministic = true;         // no usable dq_accum: the pair that needs none
   if (p.d > 128) return launch_tc_bwd_wide(p, stream);
   const bool drop = p.p_dropout > 0.f;
 #define FA_MASKED(DD, BF, DR)                                                              \

@@ -111,3 +111,51 @@ def test_tc_bwd_deterministic_is_bit_reproducible_and_correct(name):
     for t in ("dq", "dk", "dv"):
         assert np.array_equal(a[t], b[t]), t
     G.check_bwd("tc_bwd_deterministic/" + name, pb, a, rb, None)
+
+
+@pytest.mark.parametrize("variant", ["null_dq_accum", "unrounded_sizes", "d192_null_dq_accum", "packed_null_dq_accum"])
+def test_tc_bwd_without_a_usable_dq_accum(variant):
+    """A caller whose backward scratch is smaller than include/flash_attn.h sizes it -- dq_accum NULL, or the *_rounded
+    arguments not rounded (softmax_d then has exactly seqlen_q entries per row) -- still gets the tcgen05 kernels: the
+    two-launch backward needs no dq_accum (the packed dq_accum size is the one thing that
+    cannot be verified against Paddle's call site here)."""
+    import ctypes
+    import torch
+    import gpu_util as G
+    from flash_attention_hip_b200 import api
+    if variant == "packed_null_dq_accum":
+        pb = cases.varlen([300, 77, 515], [300, 77, 515], 4, 2, 128, is_causal=True, p_dropout=0.1, seed=4, offset=1)
+    else:
+        pb = cases.dense(2, 300, 450, 4, 2, 192 if variant.startswith("d192") else 128, is_causal=True, p_dropout=0.1, seed=4, offset=1)
+    q, k, v, dout = cases.make_inputs(pb, seed=42)
+    ref = O.forward(pb, q, k, v)
+    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    t = [G.to_dev(a, pb.is_bf16) for a in (dout, q, k, v, ref["out"])]
+    lse = torch.from_numpy(np.ascontiguousarray(ref["lse"], dtype=np.float32)).cuda()
+    nb = pb.batch
+    sq_r = pb.seqlen_q if variant == "unrounded_sizes" else api.round_up(pb.seqlen_q, 128)
+    d_r = pb.head_size if variant == "unrounded_sizes" else api.round_up(pb.head_size, 32)
+    g = G.Guarded()
+    softmax_d = g.make((nb, pb.num_heads, sq_r), torch.float32)
+    dq_accum = g.make((nb, sq_r, pb.num_heads, d_r), torch.float32) if variant == "unrounded_sizes" else None
+    grads = [g.make(tuple(x.shape), x.dtype) for x in (t[1], t[2], t[3])]
+    P = lambda x: None if x is None else ctypes.c_void_p(x.data_ptr())
+    L = api.lib()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    scale = pb.softmax_scale if pb.softmax_scale else pb.head_size ** -0.5
+    common = (sq_r, api.round_up(pb.seqlen_k, 128), pb.num_heads, pb.num_heads_k, pb.head_size, d_r, pb.p_dropout, scale, 1.0 / scale,
+              pb.is_causal, pb.is_bf16, 0, st, pb.seed, pb.offset, None, None)
+    if pb.varlen:
+        cq, ck = torch.from_numpy(pb.cu_seqlens_q).cuda(), torch.from_numpy(pb.cu_seqlens_k).cuda()
+        ok = L.flash_attn_varlen_bwd(P(t[0]), P(t[1]), P(t[2]), P(t[3]), P(t[4]), P(softmax_d), P(lse), P(cq), P(ck), None,
+                                     P(grads[0]), P(grads[1]), P(grads[2]), P(dq_accum), nb, pb.seqlen_q, pb.seqlen_k, *common)
+    else:
+        ok = L.flash_attn_bwd(P(t[0]), P(t[1]), P(t[2]), P(t[3]), P(t[4]), P(softmax_d), P(lse), None, P(grads[0]), P(grads[1]),
+                              P(grads[2]), P(dq_accum), nb, pb.seqlen_q, pb.seqlen_k, *common)
+    assert ok, api.last_error()
+    assert api.last_path() == api.PATH_TCGEN05
+    torch.cuda.synchronize()
+    g.check()
+    gb = dict(dq=G.to_bits(grads[0]).reshape(pb.q_shape()), dk=G.to_bits(grads[1]).reshape(pb.k_shape()),
+              dv=G.to_bits(grads[2]).reshape(pb.k_shape()))
+    G.check_bwd("tc_bwd_short_scratch/" + variant, pb, gb, rb, None)
