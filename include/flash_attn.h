@@ -22,6 +22,10 @@
  *
  * Semantics the reference header leaves open are fixed in DESIGN.md section 3
  * ("decisions") and restated briefly beside each argument here.
+ *
+ * The six prototypes restate the interface of yuguo-Jack/flash-attention-hip's
+ * flash_attn.h (BSD 3-Clause License, Copyright (c) 2024, yuguo): an ABI has to
+ * match token for token.  Everything behind them is this repository's own.
  */
 #ifndef FLASH_ATTN_B200_FLASH_ATTN_H_
 #define FLASH_ATTN_B200_FLASH_ATTN_H_
