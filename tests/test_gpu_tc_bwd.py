@@ -159,3 +159,21 @@ def test_tc_bwd_without_a_usable_dq_accum(variant):
     gb = dict(dq=G.to_bits(grads[0]).reshape(pb.q_shape()), dk=G.to_bits(grads[1]).reshape(pb.k_shape()),
               dv=G.to_bits(grads[2]).reshape(pb.k_shape()))
     G.check_bwd("tc_bwd_short_scratch/" + variant, pb, gb, rb, None)
+
+
+@pytest.mark.parametrize("scale", [-0.11, 0.0])
+@pytest.mark.parametrize("d", [64, 128, 256])
+def test_tc_bwd_non_positive_softmax_scale(scale, d):
+    """softmax_scale <= 0 is legal arithmetic.  The forward tracks its running maximum on raw scores and leaves such calls to
+    the all-shapes kernel; the backward recomputes P from the stored LSE and runs them on the tcgen05 kernels."""
+    import gpu_util as G
+    pb = cases.dense(2, 300, 333, 4, 2, d, is_causal=True, p_dropout=0.1, seed=6, offset=2, softmax_scale=scale)
+    q, k, v, dout = cases.make_inputs(pb, seed=42)
+    ref = O.forward(pb, q, k, v)
+    rb = O.backward(pb, dout, q, k, v, ref["out"], ref["lse"])
+    gb = G.run_bwd(pb, dout, q, k, v, ref["out"], ref["lse"])
+    assert gb["path"] == 2
+    G.check_bwd(f"tc_bwd/scale_{scale}_d{d}", pb, gb, rb, None)
+    f = G.run_fwd(pb, q, k, v)
+    assert f["path"] == 1                       # the forward of such a call: all-shapes kernel
+    G.check_fwd(f"generic_fwd/scale_{scale}_d{d}", pb, f, ref, None)
