@@ -116,9 +116,13 @@ bool fwd_impl(const char *fn, const void *q, const void *k, const void *v, const
   if (empty) { g_last_launches = launches; return true; }
   const bool use_tc = tc_ok && g_path_request != FA_B200_PATH_GENERIC;
   const char *err = use_tc ? fa::launch_tc_fwd(p, st) : fa::launch_generic_fwd(p, st);
+  ++launches;
+  // return_softmax beside the tcgen05 forward: a second pass over Q K^T from the LSE just written (the all-shapes
+  // kernel writes it itself)
+  if (!err && use_tc && p.softmax_ret) { err = fa::launch_softmax_ret(p, st); ++launches; }
   if (err) return fail("%s: %s", fn, err);
   g_last_path = use_tc ? FA_B200_PATH_TCGEN05 : FA_B200_PATH_GENERIC;
-  g_last_launches = launches + 1;
+  g_last_launches = launches;
   return true;
 }
 

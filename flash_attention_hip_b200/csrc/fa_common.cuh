@@ -181,7 +181,9 @@ const char *launch_mma_bwd(const Params &p, cudaStream_t stream);
 
 // tcgen05 paths; return nullptr on success, else a static error string.
 bool tc_fwd_supported(const Params &p);
-const char *launch_tc_fwd(const Params &p, cudaStream_t stream);
+const char *launch_tc_fwd(const Params &p, cudaStream_t stream);     // ignores p.softmax_ret
+// S_dmask (p.softmax_ret) from q, k, the bias and the LSE a forward has written (fa_softmax_ret.cu)
+const char *launch_softmax_ret(const Params &p, cudaStream_t stream);
 bool tc_bwd_supported(const Params &p);
 const char *launch_tc_bwd(const Params &p, cudaStream_t stream);
 const char *launch_tc_bwd_wide(const Params &p, cudaStream_t stream);   // head sizes 136..256 (fa_tc_bwd_wide.cu)

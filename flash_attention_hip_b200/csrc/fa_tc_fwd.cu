@@ -870,7 +870,6 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_fwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
-  if (p.softmax_ret) return false;               // S_dmask output: all-shapes kernel
   if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;

@@ -53,7 +53,9 @@ typedef struct CUstream_st *fa_stream_t;
  *   rng_state  2 x uint64 {seed, offset}, written when non-NULL.
  *   softmax_ptr  only when return_softmax: input dtype,
  *        [batch, num_heads, seqlen_q_rounded, seqlen_k_rounded], the
- *        normalised probabilities, negated where dropout removed the entry.
+ *        normalised probabilities, 0 where the causal mask hides the entry,
+ *        negated where dropout removed it; rows >= seqlen_q and columns >=
+ *        seqlen_k of each plane are not written.
  *   *_rounded  used only as strides of softmax_ptr / scratch, never to index
  *        q, k, v, out.
  *   p_dropout  probability to DROP, in [0, 1].

@@ -1,7 +1,7 @@
 """Dropout masks of the tcgen05 kernels, compared BIT FOR BIT with the written specification
 (csrc/philox_spec.h through oracle.dropout_mask) -- north_star: "Dropout masks must be bit-exact for a
-given seed/offset".  The ABI's own window on the mask (`return_softmax`) is served by the all-shapes
-kernel, so the kernels that ship are probed through their ordinary outputs instead:
+given seed/offset".  The ABI's own window on the mask (`return_softmax`) is written by a separate pass
+(tests/test_gpu_tc_return_softmax.py), so the kernels that ship are probed through their ordinary outputs here:
 
   forward    V = identity block at key tile j (zeros elsewhere)  =>  out[row, c] = P_drop[row, jD + c] / (1-p),
              so  out != 0  <=>  the entry is visible AND kept.
