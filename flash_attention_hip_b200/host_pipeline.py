@@ -20,7 +20,7 @@ class HostPipelinedAttention:
     """Device staging buffers + streams for one problem shape; reuse it across steps."""
 
     def __init__(self, b: int, s: int, h: int, hk: int, d: int, dtype=torch.bfloat16, chunks: int = 8,
-                 device: Optional[torch.device] = None):
+                 device: Optional[torch.device] = None, fine_events: bool = True):
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.b, self.s, self.h, self.hk, self.d = b, s, h, hk, d
         self.bounds = [(b * c // chunks, b * (c + 1) // chunks) for c in range(chunks) if b * c // chunks < b * (c + 1) // chunks]
@@ -34,6 +34,7 @@ class HostPipelinedAttention:
                          torch.empty((bc, sq_r, h, d_r), dtype=torch.float32, device=self.device)) for _ in range(2)]
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(device=self.device) for _ in range(3))
         self.launches = 0
+        self.fine_events = fine_events      # False: one event per chunk and direction (kept for A/B timing)
 
     def step(self, hq, hk, hv, hdo, ho, hdq, hdk, hdv, *, causal: bool, p_dropout: float = 0.0, seed: int = 0,
              offset: int = 0, batch_base: int = 0, scale: Optional[float] = None) -> None:
@@ -43,26 +44,34 @@ class HostPipelinedAttention:
         for st in (self.s_in, self.s_cmp, self.s_out):
             st.wait_stream(cur)
         for c, (i0, i1) in enumerate(self.bounds):
+            # the forward needs q, k, v only and its result can leave while the backward runs: two events per direction
+            # shorten the un-overlapped head (first chunk in) and tail (last chunk out) of the pipeline by a quarter each
             with torch.cuda.stream(self.s_in):
-                for dst, src in ((self.q, hq), (self.k, hk), (self.v, hv), (self.do, hdo)):
+                for dst, src in ((self.q, hq), (self.k, hk), (self.v, hv)):
                     dst[i0:i1].copy_(src[i0:i1], non_blocking=True)
-                ready = self.s_in.record_event()
-            self.s_cmp.wait_event(ready)
+                qkv_ready = self.s_in.record_event()
+                self.do[i0:i1].copy_(hdo[i0:i1], non_blocking=True)
+                do_ready = self.s_in.record_event()
             kw = dict(p_dropout=p_dropout, softmax_scale=scale, is_causal=causal, seed=seed, offset=offset,
                       stream=self.s_cmp, batch_base=batch_base + i0)
             sd, acc = self.scratch[c & 1]
             n = i1 - i0
             # torch's allocator ties lse / rng_state to the stream that is current when they are made
             with torch.cuda.stream(self.s_cmp):
+                self.s_cmp.wait_event(qkv_ready if self.fine_events else do_ready)
                 _, lse, _, _ = api.flash_attn_fwd(self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], out=self.out[i0:i1], **kw)
                 self.launches += api.last_launch_count()
+                fwd_done = self.s_cmp.record_event()
+                self.s_cmp.wait_event(do_ready)
                 api.flash_attn_bwd(self.do[i0:i1], self.q[i0:i1], self.k[i0:i1], self.v[i0:i1], self.out[i0:i1], lse,
                                    scratch=(sd[:n], acc[:n]), grads=(self.dq[i0:i1], self.dk[i0:i1], self.dv[i0:i1]),
                                    **kw)
                 self.launches += api.last_launch_count()
-            done = self.s_cmp.record_event()
-            self.s_out.wait_event(done)
+                bwd_done = self.s_cmp.record_event()
             with torch.cuda.stream(self.s_out):
-                for dst, src in ((ho, self.out), (hdq, self.dq), (hdk, self.dk), (hdv, self.dv)):
+                self.s_out.wait_event(fwd_done if self.fine_events else bwd_done)
+                ho[i0:i1].copy_(self.out[i0:i1], non_blocking=True)
+                self.s_out.wait_event(bwd_done)
+                for dst, src in ((hdq, self.dq), (hdk, self.dk), (hdv, self.dv)):
                     dst[i0:i1].copy_(src[i0:i1], non_blocking=True)
         cur.wait_stream(self.s_out)
