@@ -19,7 +19,7 @@
 //     to 16 bits on the way would cost accuracy; the 2 x 67 MB per step at S = 128k, N = 8 are ~0.15 ms of
 //     NVLink time under ~6 ms of kernels), and arrive home after the last step.
 // NCCL is bound at run time (dlopen of libnccl.so.2 -- the one already in the process when the caller is a
-// torch program): callers of the reference ABI never need it.  Dropout is not offered in this mode.
+// torch program): callers of the reference ABI never need it.  Dropout: the *_dropout entry points (step_offset below).
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -102,6 +102,14 @@ Step ring_step(bool causal, int rank, int src, int s_local) {
   if (src == rank) return {0, s_local, 0, s_local, true};
   if (src < rank) return {0, s_local, 0, c, false};
   return {c, s_local, 0, s_local, false};
+}
+
+// Dropout in ring mode (include/flash_attn_b200_ext.h): every step is an ORDINARY call with the caller's seed, its own
+// Philox offset and batch_base = the batch entry -- rows and columns counted inside the step's (query slice, K/V chunk).
+// The pair index goes into bits 48.. of the offset, i.e. into the Philox KEY (csrc/philox_spec.h: key0 = lo(seed) ^
+// hi(offset)): the N * N pairs draw from unrelated streams, the backward of a pair repeats its forward's.
+uint64_t step_offset(uint64_t offset, int rank, int src, int nranks) {
+  return offset + ((uint64_t)(rank * nranks + src) << 48);
 }
 
 // ---- final merge of the forward: N partial (out, lse) -> out, lse ---------------------------------------
@@ -317,12 +325,14 @@ size_t flash_attn_b200_ring_bwd_workspace_bytes(int nranks, int b, int s_local, 
          up256((size_t)h * s_r * 4) + up256(s_r * h * d_r * 4);
 }
 
-bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, const void *v, void *out, void *lse,
-                              void *workspace, size_t workspace_bytes, int b, int s_local, int h, int hk, int d,
-                              float softmax_scale, bool is_causal, bool is_bf16, fa_stream_t stream) {
+bool flash_attn_b200_ring_fwd_dropout(fa_ring_comm_t *c, const void *q, const void *k, const void *v, void *out, void *lse,
+                                      void *workspace, size_t workspace_bytes, int b, int s_local, int h, int hk, int d,
+                                      float softmax_scale, bool is_causal, bool is_bf16, fa_stream_t stream,
+                                      float p_dropout, uint64_t seed, uint64_t offset) {
   const char *fn = "flash_attn_b200_ring_fwd";
   const RingShape r{b, s_local, h, hk, d, is_bf16};
   FA_CALL(check_shape(fn, c, r, is_causal));
+  if (!(p_dropout >= 0.f && p_dropout <= 1.f)) return failf("%s: p_dropout must be in [0, 1]", fn);
   if (!q || !k || !v || !out || !lse || !workspace) return failf("%s: NULL pointer", fn);
   const int N = c->nranks;
   if (workspace_bytes < flash_attn_b200_ring_fwd_workspace_bytes(N, b, s_local, h, hk, d))
@@ -358,11 +368,11 @@ bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, c
     m.o[t] = o_t; m.lse[t] = l_t; m.q0[t] = sp.q0; m.rows[t] = rows;
     for (int bi = 0; bi < b; ++bi) {
       const size_t qoff = (((size_t)bi * s_local + sp.q0) * h) * d * 2, koff = (((size_t)bi * s_local + sp.k0) * hk) * d * 2;
-      if (!flash_attn_fwd(static_cast<const uint8_t *>(q) + qoff, ck + koff, cv + koff, nullptr,
-                          o_t + (size_t)bi * rows * h * d * 2, nullptr, l_t + (size_t)bi * h * rows, 1, rows, krows,
-                          (rows + 127) / 128 * 128, (krows + 127) / 128 * 128, h, hk, d, (d + 31) / 32 * 32, 0.f,
-                          softmax_scale, softmax_scale != 0.f ? 1.f / softmax_scale : 0.f, sp.causal, false, is_bf16,
-                          stream, 0, 0, nullptr, nullptr))
+      if (!flash_attn_b200_fwd_shard(bi, static_cast<const uint8_t *>(q) + qoff, ck + koff, cv + koff, nullptr,
+                                     o_t + (size_t)bi * rows * h * d * 2, nullptr, l_t + (size_t)bi * h * rows, 1, rows, krows,
+                                     (rows + 127) / 128 * 128, (krows + 127) / 128 * 128, h, hk, d, (d + 31) / 32 * 32,
+                                     p_dropout, softmax_scale, softmax_scale != 0.f ? 1.f / softmax_scale : 0.f, sp.causal,
+                                     false, is_bf16, stream, seed, step_offset(offset, c->rank, src, N), nullptr, nullptr))
         return false;
     }
     if (t + 1 < N) {
@@ -382,13 +392,15 @@ bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, c
   return true;
 }
 
-bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q, const void *k, const void *v,
-                              const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
-                              size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
-                              bool is_causal, bool is_bf16, fa_stream_t stream) {
+bool flash_attn_b200_ring_bwd_dropout(fa_ring_comm_t *c, const void *dout, const void *q, const void *k, const void *v,
+                                      const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
+                                      size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
+                                      bool is_causal, bool is_bf16, fa_stream_t stream, float p_dropout, uint64_t seed,
+                                      uint64_t offset) {
   const char *fn = "flash_attn_b200_ring_bwd";
   const RingShape r{b, s_local, h, hk, d, is_bf16};
   FA_CALL(check_shape(fn, c, r, is_causal));
+  if (!(p_dropout >= 0.f && p_dropout <= 1.f)) return failf("%s: p_dropout must be in [0, 1]", fn);
   if (!dout || !q || !k || !v || !out || !lse || !dq || !dk || !dv || !workspace) return failf("%s: NULL pointer", fn);
   const int N = c->nranks;
   if (workspace_bytes < flash_attn_b200_ring_bwd_workspace_bytes(N, b, s_local, h, hk, d))
@@ -435,11 +447,12 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q
       const size_t qoff = (((size_t)bi * s_local + sp.q0) * h) * d * 2, koff = (((size_t)bi * s_local + sp.k0) * hk) * d * 2;
       FA_CUDA(cudaMemcpy2DAsync(lse_c, (size_t)rows * 4, static_cast<const float *>(lse) + (size_t)bi * h * s_local + sp.q0,
                                 (size_t)s_local * 4, (size_t)rows * 4, h, cudaMemcpyDeviceToDevice, st));
-      if (!flash_attn_bwd(static_cast<const uint8_t *>(dout) + qoff, static_cast<const uint8_t *>(q) + qoff, ck + koff,
-                          cv + koff, static_cast<const uint8_t *>(out) + qoff, softmax_d, lse_c, nullptr, dq_t, dk_t, dv_t,
-                          dq_accum, 1, rows, krows, (rows + 127) / 128 * 128, (krows + 127) / 128 * 128, h, hk, d, (int)d_r,
-                          0.f, softmax_scale, softmax_scale != 0.f ? 1.f / softmax_scale : 0.f, sp.causal, is_bf16, 0,
-                          stream, 0, 0, nullptr, nullptr))
+      if (!flash_attn_b200_bwd_shard(bi, static_cast<const uint8_t *>(dout) + qoff, static_cast<const uint8_t *>(q) + qoff,
+                                     ck + koff, cv + koff, static_cast<const uint8_t *>(out) + qoff, softmax_d, lse_c, nullptr,
+                                     dq_t, dk_t, dv_t, dq_accum, 1, rows, krows, (rows + 127) / 128 * 128,
+                                     (krows + 127) / 128 * 128, h, hk, d, (int)d_r, p_dropout, softmax_scale,
+                                     softmax_scale != 0.f ? 1.f / softmax_scale : 0.f, sp.causal, is_bf16, 0, stream, seed,
+                                     step_offset(offset, c->rank, src, N), nullptr, nullptr))
         return false;
       FA_CALL(flash_attn_b200_cp_accumulate(dq_acc + ((size_t)bi * s_local + sp.q0) * h * d, dq_t, (int64_t)rows * h * d,
                                             is_bf16, stream));
@@ -470,6 +483,21 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q
   FA_CALL(flash_attn_b200_cp_store(dk, D[cur], (int64_t)kv_elems, is_bf16, stream));
   FA_CALL(flash_attn_b200_cp_store(dv, reinterpret_cast<float *>(D[cur]) + kv_elems, (int64_t)kv_elems, is_bf16, stream));
   return true;
+}
+
+bool flash_attn_b200_ring_fwd(fa_ring_comm_t *c, const void *q, const void *k, const void *v, void *out, void *lse,
+                              void *workspace, size_t workspace_bytes, int b, int s_local, int h, int hk, int d,
+                              float softmax_scale, bool is_causal, bool is_bf16, fa_stream_t stream) {
+  return flash_attn_b200_ring_fwd_dropout(c, q, k, v, out, lse, workspace, workspace_bytes, b, s_local, h, hk, d, softmax_scale,
+                                          is_causal, is_bf16, stream, 0.f, 0, 0);
+}
+
+bool flash_attn_b200_ring_bwd(fa_ring_comm_t *c, const void *dout, const void *q, const void *k, const void *v,
+                              const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
+                              size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
+                              bool is_causal, bool is_bf16, fa_stream_t stream) {
+  return flash_attn_b200_ring_bwd_dropout(c, dout, q, k, v, out, lse, dq, dk, dv, workspace, workspace_bytes, b, s_local, h, hk,
+                                          d, softmax_scale, is_causal, is_bf16, stream, 0.f, 0, 0);
 }
 
 }  // extern "C"

@@ -15,7 +15,10 @@ three dense calls (c = chunk length, src = owner of the visiting K/V):
   src >  r : non-causal,  q[c:2c] x kv[0:2c]     (only the late query chunk sees the visitor)
 Non-causal attention takes any contiguous sharding and calls q x kv non-causally every step.
 
-Dropout is not offered here (its stream is indexed by local coordinates); p_dropout must be 0.
+Dropout: every step is an ordinary call with the caller's seed, the offset `step_offset(offset, rank, src, world)` and
+batch_base = the batch entry, rows and columns counted inside the step's (query slice, K/V chunk).  The mask is a function
+of (seed, offset, world) -- not the unsharded call's -- and the backward of a step repeats its forward's
+(include/flash_attn_b200_ext.h; restated independently in tests/ring_ref.py).
 
 Two engines run this schedule.  On CUDA tensors (the product): the library's own C entry points
 `flash_attn_b200_ring_fwd` / `flash_attn_b200_ring_bwd` (csrc/fa_ring.cu: ncclSend / ncclRecv on a communication
@@ -59,6 +62,11 @@ class RingComm:
         L.flash_attn_b200_ring_fwd.restype = ctypes.c_bool
         L.flash_attn_b200_ring_bwd.argtypes = [vp] * 11 + [sz] + [i] * 5 + [ctypes.c_float, ctypes.c_bool, ctypes.c_bool, vp]
         L.flash_attn_b200_ring_bwd.restype = ctypes.c_bool
+        drop = [ctypes.c_float, ctypes.c_uint64, ctypes.c_uint64]           # p_dropout, seed, offset
+        L.flash_attn_b200_ring_fwd_dropout.argtypes = L.flash_attn_b200_ring_fwd.argtypes + drop
+        L.flash_attn_b200_ring_fwd_dropout.restype = ctypes.c_bool
+        L.flash_attn_b200_ring_bwd_dropout.argtypes = L.flash_attn_b200_ring_bwd.argtypes + drop
+        L.flash_attn_b200_ring_bwd_dropout.restype = ctypes.c_bool
         ident = [None]
         if self.world > 1:
             if self.rank == 0:
@@ -103,7 +111,13 @@ def close_comms() -> None:
     _COMMS.clear()
 
 
-def _c_fwd(q, k, v, causal, scale, group):
+def step_offset(offset: int, rank: int, src: int, world: int) -> int:
+    """Philox offset of the ring step (rank, src): the pair index sits in bits 48.., i.e. in the Philox key
+    (csrc/fa_ring.cu `step_offset`)."""
+    return (int(offset) + ((rank * world + src) << 48)) & 0xFFFFFFFFFFFFFFFF
+
+
+def _c_fwd(q, k, v, causal, scale, group, p_dropout=0.0, seed=0, offset=0):
     c = _comm_for(group)
     b, s, h, d = q.shape
     hk = k.shape[2]
@@ -112,15 +126,18 @@ def _c_fwd(q, k, v, causal, scale, group):
     lse = torch.empty((b, h, s), dtype=torch.float32, device=q.device)
     ws = c.workspace("fwd", b, s, h, hk, d, q.device)
     P = lambda t: ctypes.c_void_p(t.data_ptr())
-    ok = c.lib.flash_attn_b200_ring_fwd(c.handle, P(q), P(k), P(v), P(out), P(lse), P(ws), ws.numel(), b, s, h, hk, d,
-                                        scale, causal, q.dtype == torch.bfloat16,
-                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    args = (c.handle, P(q), P(k), P(v), P(out), P(lse), P(ws), ws.numel(), b, s, h, hk, d, scale, causal,
+            q.dtype == torch.bfloat16, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if p_dropout > 0:
+        ok = c.lib.flash_attn_b200_ring_fwd_dropout(*args, p_dropout, seed, offset)
+    else:
+        ok = c.lib.flash_attn_b200_ring_fwd(*args)
     if not ok:
         raise c.api.FlashAttnError("flash_attn_b200_ring_fwd failed: " + c.api.last_error())
     return out, lse
 
 
-def _c_bwd(dout, q, k, v, out, lse, causal, scale, group):
+def _c_bwd(dout, q, k, v, out, lse, causal, scale, group, p_dropout=0.0, seed=0, offset=0):
     c = _comm_for(group)
     b, s, h, d = q.shape
     hk = k.shape[2]
@@ -129,9 +146,12 @@ def _c_bwd(dout, q, k, v, out, lse, causal, scale, group):
     dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
     ws = c.workspace("bwd", b, s, h, hk, d, q.device)
     P = lambda t: ctypes.c_void_p(t.data_ptr())
-    ok = c.lib.flash_attn_b200_ring_bwd(c.handle, P(dout), P(q), P(k), P(v), P(out), P(lse), P(dq), P(dk), P(dv), P(ws),
-                                        ws.numel(), b, s, h, hk, d, scale, causal, q.dtype == torch.bfloat16,
-                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    args = (c.handle, P(dout), P(q), P(k), P(v), P(out), P(lse), P(dq), P(dk), P(dv), P(ws), ws.numel(), b, s, h, hk, d,
+            scale, causal, q.dtype == torch.bfloat16, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    if p_dropout > 0:
+        ok = c.lib.flash_attn_b200_ring_bwd_dropout(*args, p_dropout, seed, offset)
+    else:
+        ok = c.lib.flash_attn_b200_ring_bwd(*args)
     if not ok:
         raise c.api.FlashAttnError("flash_attn_b200_ring_bwd failed: " + c.api.last_error())
     return dq, dk, dv
@@ -186,7 +206,8 @@ def _steps(causal: bool, rank: int, src: int, s_local: int):
 
 
 def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: bool,
-                  scale: Optional[float] = None, group=None, ops=None):
+                  scale: Optional[float] = None, group=None, ops=None, p_dropout: float = 0.0, seed: int = 0,
+                  offset: int = 0):
     """Forward over the ring.  q [b, s_local, h, d], k/v [b, s_local, hk, d]: this rank's shard
     (zig-zag when causal).  Returns (out [b, s_local, h, d], lse fp32 [b, h, s_local]) equal to the
     rank's rows of full-sequence attention."""
@@ -195,7 +216,7 @@ def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: 
         raise ValueError("causal ring attention needs an even local length (zig-zag chunks)")
     scale = float(d) ** -0.5 if scale is None else scale
     if ops is None and q.is_cuda:
-        return _c_fwd(q, k, v, causal, scale, group)
+        return _c_fwd(q, k, v, causal, scale, group, p_dropout, seed, offset)
     ops = ops if ops is not None else CudaOps()
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     o_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
@@ -208,7 +229,8 @@ def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: 
         (q0, q1), (k0, k1), step_causal = _steps(causal, rank, src, s)
         for bi in range(b):
             o_blk, lse_blk = ops.fwd(q[bi:bi + 1, q0:q1], kv_cur[0, bi:bi + 1, k0:k1], kv_cur[1, bi:bi + 1, k0:k1],
-                                     causal=step_causal, scale=scale)
+                                     causal=step_causal, scale=scale, p_dropout=p_dropout, seed=seed,
+                                     offset=step_offset(offset, rank, src, world), batch_base=bi)
             ops.merge(o_acc[bi, q0:q1], lse_acc[bi, :, q0:q1], o_blk[0], lse_blk[0])
         _wait(reqs)
         kv_cur, kv_nxt = kv_nxt, kv_cur
@@ -218,13 +240,14 @@ def ring_attn_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, causal: 
 
 
 def ring_attn_bwd(dout: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor,
-                  lse: torch.Tensor, *, causal: bool, scale: Optional[float] = None, group=None, ops=None):
+                  lse: torch.Tensor, *, causal: bool, scale: Optional[float] = None, group=None, ops=None,
+                  p_dropout: float = 0.0, seed: int = 0, offset: int = 0):
     """Backward over the ring from the forward's (out, lse).  The dK/dV partial sums travel with
     their K/V chunk (fp32) and arrive home after the last hop.  Returns (dq, dk, dv)."""
     b, s, h, d = q.shape
     scale = float(d) ** -0.5 if scale is None else scale
     if ops is None and q.is_cuda:
-        return _c_bwd(dout, q, k, v, out, lse, causal, scale, group)
+        return _c_bwd(dout, q, k, v, out, lse, causal, scale, group, p_dropout, seed, offset)
     ops = ops if ops is not None else CudaOps()
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     dq_acc = torch.zeros((b, s, h, d), dtype=torch.float32, device=q.device)
@@ -242,7 +265,8 @@ def ring_attn_bwd(dout: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch
             lse_b = lse[bi:bi + 1, :, q0:q1].contiguous()
             blocks.append(ops.bwd(dout[bi:bi + 1, q0:q1], q[bi:bi + 1, q0:q1], kv_cur[0, bi:bi + 1, k0:k1],
                                   kv_cur[1, bi:bi + 1, k0:k1], out[bi:bi + 1, q0:q1], lse_b,
-                                  causal=step_causal, scale=scale))
+                                  causal=step_causal, scale=scale, p_dropout=p_dropout, seed=seed,
+                                  offset=step_offset(offset, rank, src, world), batch_base=bi))
         if t > 0:                     # partial sums for the chunk held now arrive from the previous rank
             _wait(dkv_reqs)
             dkv_cur, dkv_nxt = dkv_nxt, dkv_cur

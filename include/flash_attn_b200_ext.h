@@ -114,8 +114,15 @@ bool flash_attn_b200_cp_store(void *dst, const void *src_f32, int64_t n, bool is
  * ring_bwd takes the forward's (out, lse) and returns dq, dk, dv of the shard.  K/V chunks (and, in the backward,
  * the fp32 dK/dV partial sums) travel round the ring with ncclSend / ncclRecv on a communication stream owned by the
  * comm object, one step ahead of the kernels that consume them; everything else is enqueued on `stream`.  Every
- * rank must make the same call.  No dropout, no attn_mask in this mode.  NCCL is bound at run time (dlopen of
+ * rank must make the same call.  No attn_mask in this mode.  NCCL is bound at run time (dlopen of
  * libnccl.so.2): nothing else in this library needs it.
+ *
+ * Dropout (the *_dropout pair; p_dropout = 0 is exactly ring_fwd / ring_bwd): the step of rank r on the K/V chunk of
+ * rank src is an ordinary call with the caller's seed, offset + ((r * N + src) << 48) and batch_base = the batch entry,
+ * rows and columns counted inside that step's (query slice, K/V chunk) -- see csrc/fa_ring.cu for the slices.  The mask
+ * is therefore a function of (seed, offset, N) and NOT the unsharded call's (as in every ring attention built on
+ * per-block calls); forward and backward of one pair draw the same mask; a checker can replay any rank's steps with the
+ * ordinary entry points on one GPU (tests/test_gpu_shard_ring.py).
  *
  * Bootstrap like NCCL's own: one rank calls ring_unique_id, hands the FA_B200_RING_ID_BYTES to the others by any
  * means, every rank (its device current) calls ring_comm_create.  ring_comm_from_nccl borrows a communicator the
@@ -136,6 +143,15 @@ bool flash_attn_b200_ring_bwd(fa_ring_comm_t *comm, const void *dout, const void
                               const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
                               size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
                               bool is_causal, bool is_bf16, fa_stream_t stream);
+bool flash_attn_b200_ring_fwd_dropout(fa_ring_comm_t *comm, const void *q, const void *k, const void *v, void *out,
+                                      void *lse, void *workspace, size_t workspace_bytes, int b, int s_local, int h, int hk,
+                                      int d, float softmax_scale, bool is_causal, bool is_bf16, fa_stream_t stream,
+                                      float p_dropout, uint64_t seed, uint64_t offset);
+bool flash_attn_b200_ring_bwd_dropout(fa_ring_comm_t *comm, const void *dout, const void *q, const void *k, const void *v,
+                                      const void *out, const void *lse, void *dq, void *dk, void *dv, void *workspace,
+                                      size_t workspace_bytes, int b, int s_local, int h, int hk, int d, float softmax_scale,
+                                      bool is_causal, bool is_bf16, fa_stream_t stream, float p_dropout, uint64_t seed,
+                                      uint64_t offset);
 
 /* Developer builds only (-DFA_TRACE): copies the in-kernel event timeline of warp role `role`
  * of the forward (kernel 0) or backward (kernel 1) tcgen05 kernel's traced CTA into dst as

@@ -136,3 +136,49 @@ def test_ring_c_entry_points_multi_gpu(world):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("parity OK") == world, r.stdout[-3000:]
+
+
+def test_ring_dropout_multi_gpu():
+    """Dropout in ring mode (flash_attn_b200_ring_fwd_dropout / _bwd_dropout) over 2 GPUs: every rank's rows against the
+    host-side restatement of the written per-step masks (tests/ring_ref.py) and against the Python schedule
+    (tests/cuda/ring_dropout_check.py).  Skipped where fewer GPUs are visible; the gloo test
+    tests/test_multi_rank_cpu.py checks the same specification on CPU."""
+    import subprocess
+    import sys
+    import torch
+    world = 2
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", "29547", os.path.join(root, "tests", "cuda", "ring_dropout_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("dropout parity OK") == 2 * world, r.stdout[-3000:]
+
+
+def test_ring_dropout_world1_equals_plain_call_with_the_step_offset():
+    """World size 1: the one step of the ring IS the plain call with step_offset(offset, 0, 0, 1) = offset and
+    batch_base = the batch entry -- the dropout entry points against the ordinary ones, bit for bit on the forward."""
+    import torch.distributed as dist
+    from flash_attention_hip_b200 import api, ring
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("gloo", rank=0, world_size=1)
+    try:
+        b, s, h, hk, d = 3, 384, 4, 2, 128
+        q, k, v, do = _rand((b, s, h, d), 15), _rand((b, s, hk, d), 16), _rand((b, s, hk, d), 17), _rand((b, s, h, d), 18)
+        kw = dict(p_dropout=0.25, seed=2**40 + 1, offset=2**33 + 2)
+        for causal in (True, False):
+            out, lse, _, _ = api.flash_attn_fwd(q, k, v, is_causal=causal, **kw)
+            dq, dk, dv = api.flash_attn_bwd(do, q, k, v, out, lse, is_causal=causal, **kw)
+            o2, l2 = ring.ring_attn_fwd(q, k, v, causal=causal, **kw)
+            assert torch.equal(o2, out) and torch.allclose(l2, lse, atol=1e-6)
+            g2 = ring.ring_attn_bwd(do, q, k, v, o2, l2, causal=causal, **kw)
+            for got, ref in zip(g2, (dq, dk, dv)):
+                assert float((got.float() - ref.float()).abs().max() / ref.float().abs().max()) < 2e-3
+            o0, _ = ring.ring_attn_fwd(q, k, v, causal=causal)
+            assert not torch.equal(o0, out)          # and it is a different result from the call without dropout
+    finally:
+        ring.close_comms()
+        dist.destroy_process_group()

@@ -142,6 +142,54 @@ def test_ring_attention_gloo_matches_full_sequence_oracle(world, causal):
             assert errs[name] < 2e-2, errs           # north_star: 2e-2 relative
 
 
+def _ring_dropout_worker(rank, world, port, causal, ret):
+    _init(rank, world, port)
+    try:
+        import ring_ref
+        from cpu_ops import OracleOps
+        from flash_attention_hip_b200 import ring
+        b, h, hk, d = 2, 4, 2, 32
+        s = 2 * world * 24
+        q, k, v, do = _full_problem(9 + world, b, s, h, hk, d)
+        scale = d ** -0.5
+        kw = dict(p_dropout=0.3, seed=2**40 + 11, offset=2**33 + 5)
+        # the reference never runs the ring: full-sequence float64 attention under the keep mask assembled from the
+        # per-step masks of the written specification (tests/ring_ref.py)
+        ref = ring_ref.full_reference(*(x.float().numpy() for x in (q, k, v, do)), scale, causal, world, **kw)
+        ref = {n: torch.from_numpy(a).float() for n, a in ref.items()}
+        if causal:
+            loc = lambda x, dim=1: ring.zigzag_shard(x, rank, world, dim)
+        else:
+            loc = lambda x, dim=1: x.chunk(world, dim=dim)[rank].contiguous()
+        ops = OracleOps()
+        ql, kl, vl, dol = loc(q), loc(k), loc(v), loc(do)
+        out, lse = ring.ring_attn_fwd(ql, kl, vl, causal=causal, scale=scale, ops=ops, **kw)
+        dq, dk, dv = ring.ring_attn_bwd(dol, ql, kl, vl, out, lse, causal=causal, scale=scale, ops=ops, **kw)
+        errs = {"out": _rel(out, loc(ref["out"])), "dq": _rel(dq, loc(ref["dq"])), "dk": _rel(dk, loc(ref["dk"])),
+                "dv": _rel(dv, loc(ref["dv"])), "lse": float((lse - loc(ref["lse"], 2)).abs().max())}
+        # and the mask is NOT the unsharded call's (documented): the plain oracle call must differ visibly
+        plain, _ = ops.fwd(q, k, v, causal=causal, scale=scale, **kw)
+        errs["differs_from_unsharded"] = _rel(out, loc(plain))
+        all_errs = [None] * world
+        dist.all_gather_object(all_errs, errs)
+        if rank == 0:
+            ret.put(all_errs)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,causal", [(2, True), (2, False), (3, True)])
+def test_ring_attention_gloo_with_dropout_matches_the_written_step_masks(world, causal):
+    ctx = mp.get_context("spawn")
+    ret = ctx.SimpleQueue()
+    mp.spawn(_ring_dropout_worker, args=(world, _free_port(), causal, ret), nprocs=world, join=True)
+    for errs in ret.get():
+        assert errs["lse"] < 1e-3, errs
+        for name in ("out", "dq", "dk", "dv"):
+            assert errs[name] < 2e-2, errs
+        assert errs["differs_from_unsharded"] > 0.1, errs
+
+
 def test_zigzag_roundtrip():
     from flash_attention_hip_b200 import ring
     x = torch.arange(2 * 48 * 3).reshape(2, 48, 3)
