@@ -179,3 +179,35 @@ def test_config4_full_mix_sampled_units(d, causal, p_drop):
         tag = f"{label}/seq{b}(n={n})/hk{hk}"
         parity.check(tag, "dk", dk[sl, hk].float().cpu().numpy(), rdk.cpu().numpy(), ldk.bfloat16().float().cpu().numpy())
         parity.check(tag, "dv", dv[sl, hk].float().cpu().numpy(), rdv.cpu().numpy(), ldv.bfloat16().float().cpu().numpy())
+
+
+@pytest.mark.parametrize("d,hk", [(128, 1), (64, 2), (256, 2)])
+def test_return_softmax_long_sequence(d, hk):
+    """`return_softmax` at S = 4096 (32 key tiles: the K ring and the two S accumulators of csrc/fa_softmax_ret.cu wrap many
+    times): every head's plane against fp32 math on the device (1e-2 absolute), hidden entries exactly zero, signs against
+    the oracle's Philox for one head, and out / LSE bit-equal to the call without the flag."""
+    from flash_attention_hip_b200 import api
+    b, h, s = 1, 2, 4096
+    q = _rand((b, s, h, d), 31)
+    k, v = _rand((b, s, hk, d), 32), _rand((b, s, hk, d), 33)
+    kw = dict(p_dropout=0.2, is_causal=True, seed=2**40 + 5, offset=2**33 + 1)
+    out0, lse0, _, _ = api.flash_attn_fwd(q, k, v, **kw)
+    out, lse, sm, _ = api.flash_attn_fwd(q, k, v, return_softmax=True, **kw)
+    assert api.last_path() == api.PATH_TCGEN05
+    assert torch.equal(out, out0) and torch.equal(lse.view(torch.int32), lse0.view(torch.int32))
+    hidden = torch.ones(s, s, dtype=torch.bool, device="cuda").triu(1)
+    for hh in range(h):
+        sc = (q[0, :, hh].float() @ k[0, :, hh // (h // hk)].float().t()) * d ** -0.5
+        p_ref = torch.exp(sc.masked_fill(hidden, float("-inf")) - lse[0, hh][:, None])
+        plane = sm[0, hh, :s, :s].float()
+        assert not plane[hidden].any()
+        assert float((plane.abs() - p_ref).abs().max()) < 1e-2
+        # kept |P| / (1 - p) times V reproduces the kernel's own output
+        recon = (plane.clamp_min(0) / 0.8) @ v[0, :, hh // (h // hk)].float()
+        assert _rel(out[0, :, hh], recon) < TOL_REL
+    keep = torch.from_numpy(O.dropout_mask(kw["seed"], kw["offset"], 0.2, 1, s, s).astype(bool)).cuda()   # head 1 of batch 0
+    plane = sm[0, 1, :s, :s].float()
+    nz = plane != 0
+    assert torch.equal((plane > 0)[nz], keep[nz])
+    frac = float((plane[~hidden] > 0).float().mean())
+    assert abs(frac - 205 / 256) < 5e-3            # threshold round(0.8 * 256) = 205
