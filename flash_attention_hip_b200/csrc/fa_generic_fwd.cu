@@ -1,7 +1,7 @@
 // fa_generic_fwd.cu -- all-shapes forward kernel (plain SIMT, fp32 math).
 //
 // Serves the part of the flash_attn.h ABI (reference flash_attn.h:10-66) that
-// the tcgen05 kernel does not take (softmax_scale <= 0) and the tests' forced
+// the tcgen05 kernel does not take (softmax_scale == 0) and the tests' forced
 // second implementation: any head size, attn_mask bias, return_softmax.  One warp owns one query row; lanes own keys
 // for the scores and output columns for P.V, so every global read is either a
 // full contiguous row per lane (K) or a coalesced row segment per warp (V).

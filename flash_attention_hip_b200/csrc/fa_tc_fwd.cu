@@ -158,7 +158,8 @@ struct TcFwdArgs {
   int mask_b, mask_h;    // mask_sq / mask_sk = max_seqlen_q / max_seqlen_k, entry (row, col) counted from the sequence's start
   int mask_sq, mask_sk;
   int d;                 // real head_size (<= D, multiple of 8); columns [d, D) are TMA zero fill
-  float scale_log2;      // softmax_scale * log2(e)
+  float scale_log2;      // |softmax_scale| * log2(e)
+  uint32_t qk_negate;    // softmax_scale < 0: the instruction descriptor's negate-A bit, so S = -(Q K^T) and the scale stays positive
   float rp_dropout;
   uint32_t drop_threshold;
   uint32_t key0, key1, ctr3;   // Philox key / counter word 3 (csrc/philox_spec.h)
@@ -383,7 +384,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant_
         for (int ks = 0; ks < D / 16; ++ks) {
           const uint32_t off = (ks / 4) * C::kSubBytes + (ks % 4) * 32;
           ptx::mma_ss(tmem + t * 128, ptx::smem_desc_at(hi_k, b16 + t * (C::kTileBytes >> 4), C::kSmemQ + off),
-                      ptx::smem_desc_at(hi_k, ka16, C::kSmemK + off), idesc_qk, ks > 0);
+                      ptx::smem_desc_at(hi_k, ka16, C::kSmemK + off), idesc_qk | a.qk_negate, ks > 0);
         }
       };
       // O_t (+)= P_t V: the two 64-key halves of P arrive separately (p_lo, p_hi)
@@ -870,7 +871,7 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_fwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
-  if (!(p.scale > 0.f)) return false;            // running max is tracked on raw scores
+  if (!(p.scale > 0.f || p.scale < 0.f)) return false;   // 0 / NaN: all-shapes kernel (a negative scale rides the MMA's negate-A bit)
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;
 }
@@ -913,7 +914,8 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.o_head = gqa_pack ? (long long)group * p.d : (long long)p.d;
   a.d = p.d;
   a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h; a.mask_sq = (int)p.mask_sq; a.mask_sk = (int)p.mask_sk;
-  a.scale_log2 = p.scale * kLog2e;
+  a.scale_log2 = fabsf(p.scale) * kLog2e;        // the running max is tracked on raw scores: they are negated instead
+  a.qk_negate = p.scale < 0.f ? (1u << 13) : 0u;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
   a.key0 = (uint32_t)p.seed ^ (uint32_t)(p.offset >> 32);

@@ -109,3 +109,29 @@ def test_tc_fwd_matches_generic_dropout_pattern():
         api.set_path(api.PATH_AUTO)
     assert b["path"] == 1
     assert cases.rel_err(G.f32(a["out"], pb), G.f32(b["out"], pb)) < 1.5e-2
+
+
+@pytest.mark.parametrize("kind", ["dense_bias_drop", "packed", "return_softmax"])
+def test_tc_fwd_negative_softmax_scale(kind):
+    """softmax_scale < 0 (attention to the LEAST similar keys) on the tcgen05 forward: the scores are negated by the MMA
+    (negate-A bit) and the scale made positive, so the running maximum stays a maximum.  With a bias (added after
+    scaling, unaffected), dropout, packed inputs, and through the S_dmask pass."""
+    import gpu_util as G
+    from flash_attention_hip_b200 import api
+    if kind == "dense_bias_drop":
+        pb = cases.dense(2, 260, 400, 4, 2, 128, is_causal=True, p_dropout=0.2, seed=3, offset=2**33, softmax_scale=-0.09)
+        rng = np.random.default_rng(8)
+        pb.attn_mask = O.to_storage(rng.standard_normal((1, 4, 260, 400), dtype=np.float32), True)
+    elif kind == "packed":
+        pb = cases.varlen([300, 1, 129, 64], [300, 77, 257, 64], 4, 4, 64, is_causal=True, softmax_scale=-0.125, is_bf16=False)
+    else:
+        pb = cases.dense(1, 200, 333, 2, 1, 72, p_dropout=0.3, seed=9, softmax_scale=-0.2)
+    q, k, v, _ = cases.make_inputs(pb, seed=77, with_dout=False)
+    if kind == "return_softmax":
+        from test_gpu_tc_return_softmax import check_plane
+        check_plane("neg_scale", pb, q, k, v)
+        assert api.last_path() == api.PATH_TCGEN05
+        return
+    got = G.run_fwd(pb, q, k, v)
+    assert got["path"] == api.PATH_TCGEN05
+    G.check_fwd(f"tc_fwd/negative_scale_{kind}", pb, got, O.forward(pb, q, k, v), None)
