@@ -1,8 +1,8 @@
 // fa_generic_fwd.cu -- all-shapes forward kernel (plain SIMT, fp32 math).
 //
-// Serves the part of the flash_attn.h ABI (reference flash_attn.h:10-66) that
-// the tcgen05 kernel does not take (softmax_scale == 0) and the tests' forced
-// second implementation: any head size, attn_mask bias, return_softmax.  One warp owns one query row; lanes own keys
+// A second implementation of the forward of the flash_attn.h ABI (reference
+// flash_attn.h:10-66) for the tests (flash_attn_b200_set_path(GENERIC)) and for
+// a non-finite softmax_scale: any head size, attn_mask bias, return_softmax.  One warp owns one query row; lanes own keys
 // for the scores and output columns for P.V, so every global read is either a
 // full contiguous row per lane (K) or a coalesced row segment per warp (V).
 #include "fa_common.cuh"

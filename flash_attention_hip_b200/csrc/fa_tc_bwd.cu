@@ -1143,7 +1143,7 @@ long long tc_bwd_scratch_floats(const Params &p) {
 bool tc_bwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
   // (any finite softmax_scale, zero and negative included: P is recomputed from the stored LSE, no running maximum is
-  // tracked here -- the forward, which tracks one on raw scores, needs softmax_scale != 0)
+  // tracked here -- the forward, which tracks one on raw scores, takes it through a negated MMA operand or, for zero, a 1e-30 stand-in)
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;                                          // (a scratch pair below the contract: two launches, see scratch_fits)
 }

@@ -871,7 +871,7 @@ int trace_read_fwd(unsigned long long *dst, int role, int max_events) {
 
 bool tc_fwd_supported(const Params &p) {
   if (p.d <= 0 || p.d > 256 || p.d % 8) return false;   // d is padded to 64, 128 or 256 by TMA zero fill
-  if (!(p.scale > 0.f || p.scale < 0.f)) return false;   // 0 / NaN: all-shapes kernel (a negative scale rides the MMA's negate-A bit)
+  if (!isfinite(p.scale)) return false;          // (negative: the MMA's negate-A bit; zero: see launch_tc_fwd_t)
   if (p.sq <= 0 || p.sk <= 0) return false;
   return true;
 }
@@ -914,7 +914,12 @@ const char *launch_tc_fwd_t(const Params &p, cudaStream_t stream) {
   a.o_head = gqa_pack ? (long long)group * p.d : (long long)p.d;
   a.d = p.d;
   a.mask = p.mask; a.mask_b = (int)p.mask_b; a.mask_h = (int)p.mask_h; a.mask_sq = (int)p.mask_sq; a.mask_sk = (int)p.mask_sk;
-  a.scale_log2 = fabsf(p.scale) * kLog2e;        // the running max is tracked on raw scores: they are negated instead
+  // The running max is tracked on RAW scores, so the scale the kernel multiplies by must be positive: a negative
+  // softmax_scale negates the scores instead (negate-A bit of the Q K^T MMA); softmax_scale == 0 (every visible key
+  // weighs the same) runs with 1e-30: |s| * 1e-30 is below half an ulp of any fp32 exponent argument, so every
+  // exponential is exactly 1 and LSE = log(visible keys), as with 0 -- while a hidden key's -inf stays -inf (0 * -inf
+  // would be NaN).
+  a.scale_log2 = (p.scale == 0.f ? 1e-30f : fabsf(p.scale)) * kLog2e;
   a.qk_negate = p.scale < 0.f ? (1u << 13) : 0u;
   a.rp_dropout = p.rp_dropout;
   a.drop_threshold = p.drop_threshold;
