@@ -559,7 +559,7 @@ def run_ours(args, rank, local_rank, world):
         gbs = lambda nbytes: nbytes / (e2e_ms * 1e-3) / 1e9
         line["e2e"] = {"value": world * (ff + fb) / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
                        "h2d_bytes_per_step": e2e[1], "d2h_bytes_per_step": e2e[2], "ms_per_step": e2e_ms,
-                       "how": f"pinned host buffers, {args.e2e_chunks} batch chunks pipelined on 3 streams (H2D | kernels | D2H)",
+                       "how": f"pinned host buffers, {args.e2e_chunks} batch chunks pipelined on 3 streams (H2D | kernels | D2H; the forward starts once q, k, v are in, out leaves under the backward)",
                        "sequential_ms_per_step": e2e[3],
                        "pcie_gbs_per_gpu": {"h2d": gbs(e2e[1]), "d2h": gbs(e2e[2]),
                                             "note": "achieved per direction per GPU over the whole step; the step is "
